@@ -1,0 +1,133 @@
+"""ctypes front end of the CPU oracle (``oracle/padne_oracle.c``).  TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
+reference`` legs may import this module, and only as the checker or the timed CPU baseline.
+``padne_b200/`` never imports it.
+
+Parity status: PINNED (see the header of ``padne_oracle.c`` and ``tests/test_oracle.py``).
+
+The linear solve of the reference is third-party code that is not vendored in ``/root/reference``:
+``scipy.sparse.linalg.spsolve`` (SuperLU), declared as ``scipy>=1.15.0`` in the reference's
+``pyproject.toml:46`` with no lock file; this image has scipy 1.18.1.  :func:`solve` calls it
+exactly the way ``padne/solver.py:772-779`` does, so the oracle for the solve IS the reference's
+own solver call on the identical matrix.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SRC = os.path.join(_HERE, "padne_oracle.c")
+_LIB = os.path.join(_HERE, "_build", "libpadne_oracle.so")
+_lib = None
+
+STATUS = {0: "ok", 1: "invalid argument", 2: "degenerate triangle (ZeroDivisionError)",
+          7: "non-manifold mesh", 8: "out of memory"}
+
+
+class OracleError(RuntimeError):
+    def __init__(self, code):
+        super().__init__(f"oracle status {code}: {STATUS.get(code, '?')}")
+        self.code = code
+
+
+def build(force: bool = False) -> str:
+    """Compile the C restatement with gcc (no FMA contraction).  Returns the .so path."""
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(_SRC):
+        os.makedirs(os.path.dirname(_LIB), exist_ok=True)
+        subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wall",
+                               "-o", _LIB, _SRC, "-lm"])
+    return _LIB
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        lib = ctypes.CDLL(build())
+        P = ctypes.c_void_p
+        lib.oracle_assemble.argtypes = [ctypes.c_int32, P, P, P, P, P, ctypes.c_int64, ctypes.c_int64,
+                                        P, P, P, P, ctypes.POINTER(P), ctypes.POINTER(ctypes.c_int64)]
+        lib.oracle_system_csr.argtypes = [P, P, P, P]
+        lib.oracle_system_free.argtypes = [P]
+        lib.oracle_system_free.restype = None
+        lib.oracle_corner_weights.argtypes = [ctypes.c_int64, P, ctypes.c_int64, P, P]
+        lib.oracle_power_density.argtypes = [ctypes.c_int64, P, P, ctypes.c_int64, P, ctypes.c_double, P]
+        _lib = lib
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def assemble(fs, stamps):
+    """``assemble_system`` (``solver.py:783-812``) -> ``(indptr, indices, data)`` of ``L.tocsr()``.
+
+    ``fs`` is a ``padne_b200.flat.FlatSystem``; ``stamps`` is ``(s_row, s_col, s_val, s_op)`` from
+    ``padne_b200.stamps.build_stamps``.
+    """
+    lib = _load()
+    s_row, s_col, s_val, s_op = [np.ascontiguousarray(a) for a in stamps[:4]]
+    h = ctypes.c_void_p()
+    nnz = ctypes.c_int64()
+    rc = lib.oracle_assemble(fs.n_mesh, _p(fs.v_off), _p(fs.xy), _p(fs.t_off), _p(fs.tri),
+                             _p(fs.conductance), fs.N, s_row.shape[0], _p(s_row), _p(s_col),
+                             _p(s_val), _p(s_op), ctypes.byref(h), ctypes.byref(nnz))
+    if rc:
+        raise OracleError(rc)
+    try:
+        indptr = np.empty(fs.N + 1, np.int32)
+        indices = np.empty(nnz.value, np.int32)
+        data = np.empty(nnz.value, np.float64)
+        lib.oracle_system_csr(h, _p(indptr), _p(indices), _p(data))
+    finally:
+        lib.oracle_system_free(h)
+    return indptr, indices, data
+
+
+def corner_weights(xy, tri):
+    """Per-triangle, per-corner ``abs(dot/cross)/2`` (``mesh.py:136-138``); ``tri`` indexes ``xy``."""
+    lib = _load()
+    xy = np.ascontiguousarray(xy, np.float64)
+    tri = np.ascontiguousarray(tri, np.int32)
+    w = np.empty((tri.shape[0], 3), np.float64)
+    rc = lib.oracle_corner_weights(xy.shape[0], _p(xy), tri.shape[0], _p(tri), _p(w))
+    if rc:
+        raise OracleError(rc)
+    return w
+
+
+def power_density(xy, values, tri, conductivity):
+    """``compute_power_density`` (``solver.py:728-745``) per face."""
+    lib = _load()
+    xy = np.ascontiguousarray(xy, np.float64)
+    values = np.ascontiguousarray(values, np.float64)
+    tri = np.ascontiguousarray(tri, np.int32)
+    p = np.empty(tri.shape[0], np.float64)
+    rc = lib.oracle_power_density(xy.shape[0], _p(xy), _p(values), tri.shape[0], _p(tri),
+                                  float(conductivity), _p(p))
+    if rc:
+        raise OracleError(rc)
+    return p
+
+
+def solve(indptr, indices, data, r):
+    """``solve_system`` (``solver.py:767-780``): ``(v, residual_norm, ground_node_current)``."""
+    import scipy.sparse
+    import scipy.sparse.linalg
+    n = len(indptr) - 1
+    L_csc = scipy.sparse.csr_matrix((data, indices, indptr), shape=(n, n)).tocsc()
+    v = scipy.sparse.linalg.spsolve(L_csc, r)
+    residual_norm = float(np.linalg.norm(L_csc @ v - r))
+    return v, residual_norm, float(v[-1])
+
+
+def assemble_and_solve(fs, stamps_and_rhs):
+    """The whole reference hot path on one flat system (used as the timed CPU baseline 'port')."""
+    indptr, indices, data = assemble(fs, stamps_and_rhs[:4])
+    v, res, ig = solve(indptr, indices, data, stamps_and_rhs[4])
+    return (indptr, indices, data), v, res, ig
