@@ -1,0 +1,154 @@
+/*
+ * padne_b200.h -- C ABI of the B200-native padne FEM hot path (libpadne_b200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch or
+ * Python types.  Every entry point names the reference interface it replaces; paths are relative
+ * to the reference repository (atx/padne).
+ *
+ * Conventions
+ *   - every function returns an int status, PDN_OK == 0 (pdn_strerror() gives the text);
+ *   - all array arguments are caller-owned and only borrowed for the duration of the call;
+ *   - `on_device != 0` means every ARRAY pointer of that call is a device pointer on the context's
+ *     GPU (e.g. a torch tensor's data_ptr()); otherwise they are host pointers and the call does
+ *     the host<->device copies itself;
+ *   - one in-flight call per pdn_ctx (the reference is single-threaded, solver.py:783-812);
+ *   - the assembled system stays RESIDENT on the device inside the context between
+ *     pdn_assemble / pdn_set_csr and pdn_solve, so the solve needs no second upload.
+ *
+ * Unknown order (padne/solver.py:757-760):
+ *   [ mesh vertices | internal network nodes | one current per VoltageSource/VoltageRegulator |
+ *     ground current ]            n_nodes = vertices + internal nodes;  N = n_nodes + extras + 1
+ */
+#ifndef PADNE_B200_H
+#define PADNE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes -> the exception the Python shim raises (reference behaviour in brackets) */
+#define PDN_OK 0
+#define PDN_EINVAL 1        /* ValueError                                                         */
+#define PDN_EDEGENERATE 2   /* ZeroDivisionError  [HalfEdge.cotan, padne/mesh.py:138]             */
+#define PDN_ESINGULAR 3     /* singular / inconsistent constraints [SuperLU: "Matrix is exactly   */
+                            /* singular" warning and an all-NaN v]                                */
+#define PDN_ENOTCONVERGED 4 /* RuntimeError: Krylov solver hit max_iter (never silent)            */
+#define PDN_ECUDA 5         /* RuntimeError: CUDA / NCCL failure                                  */
+#define PDN_EUNSUPPORTED 6  /* NotImplementedError [padne/solver.py:454-456, 540-541]             */
+#define PDN_ENONMANIFOLD 7  /* ValueError("Non-manifold mesh") [padne/mesh.py:343]                */
+#define PDN_ENOMEM 8        /* MemoryError                                                        */
+#define PDN_ENOSYSTEM 9     /* RuntimeError: no resident system (call pdn_assemble/pdn_set_csr)   */
+
+/* stamp operations: scipy lil_matrix `+=` versus `=` (padne/solver.py:480-484 vs :503-511) */
+#define PDN_OP_ADD 0
+#define PDN_OP_SET 1
+
+/* Krylov methods (pdn_opts.method / pdn_info.method) */
+#define PDN_METHOD_AUTO 0     /* PCG when the reduced system is symmetric, else BiCGSTAB          */
+#define PDN_METHOD_PCG 1
+#define PDN_METHOD_BICGSTAB 2
+
+/* preconditioners */
+#define PDN_PRECOND_JACOBI 0
+#define PDN_PRECOND_NONE 1
+#define PDN_PRECOND_AMG 2     /* aggregation multigrid V-cycle with Jacobi smoothing              */
+
+typedef struct pdn_ctx pdn_ctx;
+
+typedef struct pdn_opts {
+    double rtol;        /* stop when ||b - A u||_2 <= rtol * ||b||_2 on the reduced system; 0 -> 1e-10 */
+    double atol;        /* ... or <= atol (absolute); 0 -> disabled                                 */
+    int32_t max_iter;   /* 0 -> 20 * sqrt(N) + 2000                                                 */
+    int32_t method;     /* PDN_METHOD_*                                                            */
+    int32_t precond;    /* PDN_PRECOND_*                                                           */
+    int32_t check_every;/* iterations per CUDA-graph launch between host convergence polls; 0 -> 32 */
+    int64_t n_nodes;    /* voltage unknowns; <0 -> detect (trailing rows without a diagonal entry)  */
+} pdn_opts;
+
+typedef struct pdn_info {
+    int32_t method;             /* PDN_METHOD_PCG or PDN_METHOD_BICGSTAB actually used             */
+    int32_t iterations;
+    int32_t restarts;           /* true-residual restarts                                          */
+    int32_t n_constraints;      /* extra unknowns eliminated                                       */
+    double rel_residual;        /* ||b - A u|| / ||b|| of the reduced system (true residual)       */
+    double residual_norm;       /* ||L v - r||_2 of the FULL system, as padne/solver.py:775        */
+    double ground_node_current; /* v[N-1], padne/solver.py:777                                      */
+    double t_setup_ms;          /* constraint elimination + reduced operator                        */
+    double t_krylov_ms;         /* Krylov iterations (CUDA events)                                  */
+    double t_total_ms;
+    double spmv_ms;             /* mean duration of one reduced-operator SpMV launch, measured by   */
+                                /* pdn_bench_spmv-style events during the solve (0 if not measured) */
+} pdn_info;
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* One context = one GPU, one stream, one resident system.  `device` is the CUDA ordinal. */
+int pdn_create(pdn_ctx **out, int device);
+int pdn_destroy(pdn_ctx *ctx);
+const char *pdn_strerror(int status);
+/* Text of the last CUDA/NCCL failure or argument complaint on this context ("" if none). */
+const char *pdn_last_error(pdn_ctx *ctx);
+/* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */
+int64_t pdn_launch_count(pdn_ctx *ctx);
+/* cudaStream_t of the context as an integer, so callers can record CUDA events on it. */
+uint64_t pdn_stream(pdn_ctx *ctx);
+
+/* ---- kernel (1): element weights --------------------------------------------------------------
+ * Replaces HalfEdge.cotan (padne/mesh.py:124-139): w[t][c] = abs(dot/cross)/2 at corner c of
+ * triangle t, i.e. the contribution of face t to the weight of the edge opposite corner c.
+ * fp64, every * + - / rounded separately (no FMA), like CPython.
+ * tri indexes xy directly.  A zero cross product -> PDN_EDEGENERATE. */
+int pdn_element_weights(pdn_ctx *ctx, int64_t n_v, const double *xy /*[n_v,2]*/, int64_t n_t,
+                        const int32_t *tri /*[n_t,3]*/, double *w /*[n_t,3]*/, int on_device);
+
+/* ---- kernels (1)+(2): global assembly -----------------------------------------------------------
+ * Replaces assemble_system (padne/solver.py:783-812) = laplace_operator per mesh (:171-213) scaled
+ * by the mesh conductance and scattered at the VertexIndexer offset (:216-229, :563-575), then the
+ * ordered lumped-element / ground stamps (:469-560) replayed with lil_matrix semantics
+ * (an entry that becomes exactly 0.0 leaves the pattern).
+ *   v_off/t_off [n_mesh+1]: vertex / triangle offsets of each mesh (back to back);
+ *   tri: MESH-LOCAL vertex indices;  conductance [n_mesh];
+ *   s_row/s_col/s_val/s_op [n_stamp]: stamp operations in the reference's execution order.
+ * The result stays resident; *nnz_out receives the number of stored entries. */
+int pdn_assemble(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
+                 const int64_t *t_off, const int32_t *tri, const double *conductance, int64_t N,
+                 int64_t n_stamp, const int32_t *s_row, const int32_t *s_col, const double *s_val,
+                 const int32_t *s_op, int on_device, int64_t *nnz_out);
+
+/* Copy the resident CSR out (L.tocsr(): int32 sorted indices, no explicit zeros).
+ * indptr [N+1], indices [nnz], data [nnz].  Any pointer may be NULL to skip that array. */
+int pdn_get_csr(pdn_ctx *ctx, int32_t *indptr, int32_t *indices, double *data, int on_device);
+/* Shape of the resident system. */
+int pdn_get_shape(pdn_ctx *ctx, int64_t *N, int64_t *nnz);
+/* Make a caller-provided CSR the resident system (the solve_system(L, r) seam, solver.py:767). */
+int pdn_set_csr(pdn_ctx *ctx, int64_t N, int64_t nnz, const int32_t *indptr, const int32_t *indices,
+                const double *data, int on_device);
+
+/* ---- kernels (3)+(4): the solve ------------------------------------------------------------------
+ * Replaces solve_system (padne/solver.py:767-780): solves L v = rhs for the resident L.
+ * The constraint rows/columns (indices >= n_nodes) are eliminated on the host (union-find with
+ * voltage offsets), the reduced operator is solved with Jacobi-PCG (symmetric) or BiCGSTAB
+ * (regulator gains present), the eliminated currents are recovered, and the residual of the
+ * FULL system is reported exactly as solver.py:775.   rhs [N], v [N]. */
+int pdn_solve(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v, pdn_info *info,
+              int on_device);
+
+/* y = L x with the resident full system (diagnostics, tests, SpMV benchmarking). x,y [N]. */
+int pdn_spmv(pdn_ctx *ctx, const double *x, double *y, int on_device);
+/* Time `reps` launches of the solver's SpMV kernel on the resident system with CUDA events on the
+ * context stream; returns the mean milliseconds per launch.  flush_l2 != 0 writes a >L2 buffer
+ * between launches (outside the events). */
+int pdn_bench_spmv(pdn_ctx *ctx, int32_t reps, int flush_l2, double *ms_per_launch);
+
+/* ---- next row F1: per-face power density ----------------------------------------------------------
+ * Replaces compute_power_density / compute_triangle_gradient (padne/solver.py:689-745):
+ * p[t] = conductivity * |grad V|^2 with the reference's exact barycentric expression order.
+ * tri indexes xy / val directly. */
+int pdn_power_density(pdn_ctx *ctx, int64_t n_v, const double *xy, const double *val, int64_t n_t,
+                      const int32_t *tri, double conductivity, double *p /*[n_t]*/, int on_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PADNE_B200_H */

@@ -1,0 +1,179 @@
+// pdn_common.cuh -- context, device buffers, launch bookkeeping and small device-wide primitives
+// shared by the kernels of libpadne_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/padne_b200.h"
+
+// ------------------------------------------------------------------------------------------------
+// error handling
+// ------------------------------------------------------------------------------------------------
+struct pdn_error {
+    int code;
+    std::string msg;
+};
+
+#define PDN_CUDA(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            char _b[512];                                                                       \
+            snprintf(_b, sizeof _b, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr,               \
+                     cudaGetErrorString(_e));                                                   \
+            throw pdn_error{_e == cudaErrorMemoryAllocation ? PDN_ENOMEM : PDN_ECUDA, _b};      \
+        }                                                                                       \
+    } while (0)
+
+#define PDN_FAIL(code_, ...)                                                                    \
+    do {                                                                                        \
+        char _b[512];                                                                           \
+        snprintf(_b, sizeof _b, __VA_ARGS__);                                                   \
+        throw pdn_error{(code_), _b};                                                           \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// device buffer (RAII, grows only)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;  // elements
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    // contents are NOT preserved
+    T *reserve(size_t n) {
+        if (n > cap) {
+            release();
+            size_t want = n + n / 16 + 64;
+            PDN_CUDA(cudaMalloc((void **)&p, want * sizeof(T)));
+            cap = want;
+        }
+        return p;
+    }
+    void swap(DevBuf &o) {
+        T *tp = p; p = o.p; o.p = tp;
+        size_t tc = cap; cap = o.cap; o.cap = tc;
+    }
+};
+
+// A borrowed-or-staged input array: device pointer either given by the caller or uploaded.
+template <typename T>
+struct DevIn {
+    const T *p = nullptr;
+    DevBuf<T> own;
+    void set(const T *src, size_t n, bool on_device, cudaStream_t s) {
+        if (on_device || n == 0) { p = src; return; }
+        own.reserve(n);
+        PDN_CUDA(cudaMemcpyAsync(own.p, src, n * sizeof(T), cudaMemcpyHostToDevice, s));
+        p = own.p;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// resident systems
+// ------------------------------------------------------------------------------------------------
+struct CsrDev {
+    int64_t n = 0, nnz = 0;
+    DevBuf<int32_t> indptr, indices;
+    DevBuf<double> data;
+    bool valid = false;
+};
+
+struct SolveWork;  // pdn_solve.cu
+
+struct pdn_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int n_sm = 148;
+    int64_t launches = 0;
+    std::string last_error;
+    CsrDev L;                  // the full system of padne/solver.py:783-812
+    int32_t *d_status = nullptr;  // [4] device status words (error code, detail)
+    int32_t *h_status = nullptr;  // pinned mirror
+    DevBuf<char> l2_flush;
+    SolveWork *solve = nullptr;
+};
+
+#define PDN_LAUNCH(ctx, kernel, grid, block, smem, ...)                                         \
+    do {                                                                                        \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                        \
+        (ctx)->launches++;                                                                      \
+        PDN_CUDA(cudaGetLastError());                                                           \
+    } while (0)
+
+static inline int pdn_blocks(int64_t n, int block) { return (int)((n + block - 1) / block); }
+
+// grid for a grid-stride kernel: a multiple of the SM count, capped by the work available
+static inline int pdn_grid(const pdn_ctx *ctx, int64_t n, int block, int per_sm) {
+    int64_t need = (n + block - 1) / block;
+    int64_t full = (int64_t)ctx->n_sm * per_sm;
+    if (need < 1) need = 1;
+    return (int)(need < full ? need : full);
+}
+
+// wrap a C-ABI body: set device, translate exceptions to status codes
+template <typename F>
+static inline int pdn_guard(pdn_ctx *ctx, F &&body) {
+    if (!ctx) return PDN_EINVAL;
+    try {
+        PDN_CUDA(cudaSetDevice(ctx->device));
+        body();
+        return PDN_OK;
+    } catch (const pdn_error &e) {
+        ctx->last_error = e.msg;
+        cudaGetLastError();  // clear non-sticky errors
+        return e.code;
+    } catch (const std::bad_alloc &) {
+        ctx->last_error = "host allocation failed";
+        return PDN_ENOMEM;
+    }
+}
+
+// device status helpers (pdn_api.cu)
+void pdn_status_reset(pdn_ctx *ctx);
+// returns the device status code (0 if none) after synchronising the stream; detail in *detail
+int pdn_status_fetch(pdn_ctx *ctx, int64_t *detail);
+
+// device-wide exclusive scan of int32 counts into int64 or int32 offsets (pdn_scan.cu).
+// out has n+1 entries; out[n] = total.  Returns nothing; total can be read from out[n].
+void pdn_exclusive_scan_i32(pdn_ctx *ctx, const int32_t *in, int64_t n, int32_t *out);
+void pdn_exclusive_scan_i64(pdn_ctx *ctx, const int32_t *in, int64_t n, int64_t *out);
+
+// flush L2 by writing a buffer larger than it
+void pdn_flush_l2(pdn_ctx *ctx);
+
+// entry points implemented across translation units
+void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
+                       const int64_t *t_off, const int32_t *tri, const double *conductance,
+                       int64_t N, int64_t n_stamp, const int32_t *s_row, const int32_t *s_col,
+                       const double *s_val, const int32_t *s_op, bool on_device, int64_t *nnz_out);
+void pdn_element_weights_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, int64_t n_t,
+                              const int32_t *tri, double *w, bool on_device);
+void pdn_power_density_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, const double *val,
+                            int64_t n_t, const int32_t *tri, double conductivity, double *p,
+                            bool on_device);
+void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v,
+                    pdn_info *info, bool on_device);
+void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device);
+void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, bool flush_l2, double *ms);
+void pdn_solve_release(pdn_ctx *ctx);
+
+// SpMV launcher shared by solve / diagnostics (pdn_spmv.cu): y = A x, optional fused dot.
+// rows [0, n_rows); if dot_with != nullptr, block partial sums of dot_with[i]*y[i] go to partials
+// (one per block) -- see pdn_spmv.cu.
+void pdn_launch_spmv(pdn_ctx *ctx, int64_t n_rows, const int32_t *indptr, const int32_t *indices,
+                     const double *data, const double *x, double *y);

@@ -1,0 +1,365 @@
+// pdn_kernels.cuh -- kernels (3) and (4): the CSR-stream SpMV with fused dot products, the fused
+// Krylov vector updates and the Jacobi preconditioner.   Included by pdn_solve.cu only.
+//
+// Replaces scipy.sparse.linalg.spsolve at padne/solver.py:772-775 (SuperLU) by an iterative solve;
+// the operator is the reduced system  A = -(Z^T Q L Z)  described in pdn_solve.cu.
+//
+// SpMV layout ("CSR-stream"): a block owns RPB consecutive rows.  Their stored entries are one
+// contiguous range of the CSR arrays, so the block streams values (8 B) and column indices (4 B)
+// with fully coalesced loads, multiplies by the gathered x (read-only path, L1/L2 resident for
+// mesh-local numbering) into shared memory, and each thread then sums its own row out of shared
+// memory in column order.  HBM traffic is the algorithmic 12 B/nnz + 4 B/row + vectors, there is
+// no padding and no row permutation, and the per-row summation order is fixed (bit-reproducible).
+//
+// Dot products are fused into the kernel that produces their operands.  Every block writes one
+// partial per accumulator; the LAST block to finish (ticket counter) adds the partials in a
+// fixed order and runs the scalar recurrence, so reductions are deterministic and cost no launch.
+#pragma once
+
+#include "pdn_common.cuh"
+
+namespace pdnk {
+
+constexpr int RPB = 256;       // rows (= threads) per block
+constexpr int CAP = 2560;      // products staged per chunk (20 KB of shared memory)
+constexpr int MAX_PART = 2048; // upper bound on blocks that write reduction partials
+
+// device-resident scalars of one Krylov solve
+struct Scal {
+    // Chronopoulos-Gear PCG
+    double gamma, gamma_old, delta, alpha, beta, rr;
+    // BiCGSTAB
+    double rho, rho_old, omega, r0v, ts, tt;
+    // stopping
+    double tol2;       // squared absolute threshold on ||r||_2
+    double bnorm2;
+    int32_t iter, done, breakdown, first;
+    int32_t max_iter, pad0, pad1, pad2;
+    unsigned int ticket[4];
+};
+
+enum Mode { PLAIN = 0, CG = 1, BICG_V = 2, BICG_T = 3, RESID = 4 };
+
+// The reduced operator: main CSR part (rows flagged by a negative row pointer are skipped) plus a
+// tiny override CSR for the special rows (constraint terminals), handled by block 0.
+struct Operator {
+    int64_t n;                 // rows
+    const int32_t *rp;         // [n+1] row pointers; rp[i] < 0 flags a special row, offset = ~rp[i]
+    const int32_t *ci;         // column indices
+    const double *va;          // values
+    int32_t n_special;         // override rows
+    const int32_t *sp_row;     // [n_special] row index of each override row
+    const int32_t *sp_rp;      // [n_special+1]
+    const int32_t *sp_ci;
+    const double *sp_va;
+};
+
+__device__ __forceinline__ int32_t rp_decode(int32_t v) { return v < 0 ? ~v : v; }
+
+template <int NACC>
+__device__ __forceinline__ void block_reduce(double (&acc)[NACC], double (*sm)[RPB / 32]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int a = 0; a < NACC; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[a] += __shfl_down_sync(0xffffffffu, acc[a], o);
+        if (lane == 0) sm[a][warp] = acc[a];
+    }
+    __syncthreads();
+    if (warp == 0) {
+#pragma unroll
+        for (int a = 0; a < NACC; a++) {
+            double v = lane < RPB / 32 ? sm[a][lane] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            acc[a] = v;  // valid in thread 0
+        }
+    }
+    __syncthreads();
+}
+
+// Write this block's partials; returns true (to all threads) in the last block to arrive, with
+// acc[] holding the grid totals summed in block order.
+template <int NACC>
+__device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partials, unsigned int *ticket,
+                                            double (*sm)[RPB / 32]) {
+    __shared__ bool is_last;
+    block_reduce<NACC>(acc, sm);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int a = 0; a < NACC; a++) partials[a * MAX_PART + blockIdx.x] = acc[a];
+        __threadfence();
+        unsigned int t = atomicAdd(ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return false;
+    __threadfence();
+#pragma unroll
+    for (int a = 0; a < NACC; a++) {
+        double v = 0.0;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += RPB) v += __ldcg(&partials[a * MAX_PART + b]);
+        acc[a] = v;
+    }
+    block_reduce<NACC>(acc, sm);
+    if (threadIdx.x == 0) *ticket = 0u;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// SpMV with fused dots
+//   PLAIN : y = A x
+//   CG    : y = A x (x = z);   gamma = r.z, delta = z.y, rr = r.r        aux0 = r
+//   BICG_V: y = A x (x = ph);  r0v = rhat.y                               aux0 = rhat
+//   BICG_T: y = A x (x = sh);  ts = y.s, tt = y.y                         aux0 = s
+//   RESID : y = b - A x;       rr = y.y                                   aux0 = b
+// ------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(RPB) spmv_kernel(Operator A, const double *__restrict__ x,
+                                                   double *__restrict__ y, const double *__restrict__ aux0,
+                                                   Scal *sc, double *partials) {
+    __shared__ double prod[CAP];
+    __shared__ double red[3][RPB / 32];
+    if (MODE != PLAIN && MODE != RESID) {
+        if (sc->done) return;
+    }
+    double acc[3] = {0.0, 0.0, 0.0};
+    const int64_t n_blk = (A.n + RPB - 1) / RPB;
+    for (int64_t blk = blockIdx.x; blk < n_blk; blk += gridDim.x) {
+        const int64_t r0 = blk * RPB;
+        const int64_t r1 = r0 + RPB < A.n ? r0 + RPB : A.n;
+        const int64_t row = r0 + threadIdx.x;
+        int32_t lo = 0, hi = 0;
+        bool special = true;
+        if (row < r1) {
+            const int32_t v = A.rp[row];
+            special = v < 0;
+            lo = rp_decode(v);
+            hi = special ? lo : rp_decode(A.rp[row + 1]);
+        }
+        const int32_t k0 = rp_decode(A.rp[r0]), k1 = rp_decode(A.rp[r1]);
+        double sum = 0.0;
+        for (int32_t c0 = k0; c0 < k1; c0 += CAP) {
+            const int32_t c1 = c0 + CAP < k1 ? c0 + CAP : k1;
+#pragma unroll 4
+            for (int32_t k = c0 + threadIdx.x; k < c1; k += RPB)
+                prod[k - c0] = A.va[k] * __ldg(&x[A.ci[k]]);
+            __syncthreads();
+            const int32_t a = lo > c0 ? lo : c0, b = hi < c1 ? hi : c1;
+            for (int32_t k = a; k < b; k++) sum += prod[k - c0];
+            __syncthreads();
+        }
+        if (row < r1 && !special) {
+            if (MODE == PLAIN) {
+                y[row] = sum;
+            } else if (MODE == CG) {
+                const double zi = x[row], ri = aux0[row];
+                y[row] = sum;
+                acc[0] += ri * zi; acc[1] += zi * sum; acc[2] += ri * ri;
+            } else if (MODE == BICG_V) {
+                y[row] = sum;
+                acc[0] += aux0[row] * sum;
+            } else if (MODE == BICG_T) {
+                y[row] = sum;
+                acc[0] += sum * aux0[row]; acc[1] += sum * sum;
+            } else {  // RESID
+                const double ri = aux0[row] - sum;
+                y[row] = ri;
+                acc[2] += ri * ri;
+            }
+        }
+    }
+    // override rows (constraint terminals): block 0, one thread per row
+    if (blockIdx.x == 0) {
+        for (int32_t t = threadIdx.x; t < A.n_special; t += RPB) {
+            const int32_t row = A.sp_row[t];
+            double sum = 0.0;
+            for (int32_t k = A.sp_rp[t]; k < A.sp_rp[t + 1]; k++) sum += A.sp_va[k] * x[A.sp_ci[k]];
+            if (MODE == PLAIN) {
+                y[row] = sum;
+            } else if (MODE == CG) {
+                const double zi = x[row], ri = aux0[row];
+                y[row] = sum;
+                acc[0] += ri * zi; acc[1] += zi * sum; acc[2] += ri * ri;
+            } else if (MODE == BICG_V) {
+                y[row] = sum;
+                acc[0] += aux0[row] * sum;
+            } else if (MODE == BICG_T) {
+                y[row] = sum;
+                acc[0] += sum * aux0[row]; acc[1] += sum * sum;
+            } else {
+                const double ri = aux0[row] - sum;
+                y[row] = ri;
+                acc[2] += ri * ri;
+            }
+        }
+    }
+    if (MODE == PLAIN) return;
+    if (!grid_reduce<3>(acc, partials, &sc->ticket[0], red)) return;
+    if (threadIdx.x != 0) return;
+    if (MODE == CG) {
+        const double gamma = acc[0], delta = acc[1], rr = acc[2];
+        sc->rr = rr;
+        if (rr <= sc->tol2) { sc->done = 1; return; }
+        if (sc->iter >= sc->max_iter) { sc->done = 2; return; }
+        double beta, alpha;
+        if (sc->first) {
+            beta = 0.0;
+            alpha = gamma / delta;
+            sc->first = 0;
+        } else {
+            beta = gamma / sc->gamma_old;
+            alpha = gamma / (delta - beta * gamma / sc->alpha);
+        }
+        if (!(alpha == alpha) || !(fabs(alpha) < 1e300) || delta <= 0.0) { sc->breakdown = 1; sc->done = 3; return; }
+        sc->gamma_old = gamma;
+        sc->gamma = gamma; sc->delta = delta;
+        sc->alpha = alpha; sc->beta = beta;
+        sc->iter += 1;
+    } else if (MODE == BICG_V) {
+        sc->r0v = acc[0];
+        const double alpha = sc->rho / acc[0];
+        if (!(alpha == alpha) || !(fabs(alpha) < 1e300)) { sc->breakdown = 1; sc->done = 3; return; }
+        sc->alpha = alpha;
+    } else if (MODE == BICG_T) {
+        sc->ts = acc[0]; sc->tt = acc[1];
+        const double omega = acc[1] > 0.0 ? acc[0] / acc[1] : 0.0;
+        sc->omega = omega;
+    } else if (MODE == RESID) {
+        sc->rr = acc[2];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused vector kernels (grid-stride, one element per thread per step)
+// ------------------------------------------------------------------------------------------------
+// Chronopoulos-Gear update:  p = z + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  z = dinv r
+__global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t n, const Scal *__restrict__ sc,
+                                                        const double *__restrict__ dinv,
+                                                        const double *__restrict__ w, double *__restrict__ z,
+                                                        double *__restrict__ p, double *__restrict__ s,
+                                                        double *__restrict__ x, double *__restrict__ r) {
+    if (sc->done) return;
+    const double alpha = sc->alpha, beta = sc->beta;
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        const double pi = z[i] + beta * p[i];
+        const double si = w[i] + beta * s[i];
+        const double ri = r[i] - alpha * si;
+        p[i] = pi;
+        s[i] = si;
+        x[i] += alpha * pi;
+        r[i] = ri;
+        z[i] = dinv[i] * ri;
+    }
+}
+
+// r = b (x = 0 start) or given r;  z = dinv r;  p = s = 0
+__global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t n, const double *__restrict__ dinv,
+                                                      const double *__restrict__ r, double *__restrict__ z,
+                                                      double *__restrict__ p, double *__restrict__ s) {
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        z[i] = dinv[i] * r[i];
+        p[i] = 0.0;
+        s[i] = 0.0;
+    }
+}
+
+// BiCGSTAB step 2:  s = r - alpha v;  sh = dinv s
+__global__ void __launch_bounds__(RPB) bicg_s_kernel(int64_t n, const Scal *__restrict__ sc,
+                                                     const double *__restrict__ dinv,
+                                                     const double *__restrict__ r, const double *__restrict__ v,
+                                                     double *__restrict__ s, double *__restrict__ sh) {
+    if (sc->done) return;
+    const double alpha = sc->alpha;
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        const double si = r[i] - alpha * v[i];
+        s[i] = si;
+        sh[i] = dinv[i] * si;
+    }
+}
+
+// BiCGSTAB step 4:  x += alpha ph + omega sh;  r = s - omega t;  rho_new = rhat.r;  rr = r.r
+__global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t n, Scal *sc, const double *__restrict__ ph,
+                                                     const double *__restrict__ sh, const double *__restrict__ s,
+                                                     const double *__restrict__ t, const double *__restrict__ rhat,
+                                                     double *__restrict__ x, double *__restrict__ r,
+                                                     double *partials) {
+    __shared__ double red[3][RPB / 32];
+    if (sc->done) return;
+    const double alpha = sc->alpha, omega = sc->omega;
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        x[i] += alpha * ph[i] + omega * sh[i];
+        const double ri = s[i] - omega * t[i];
+        r[i] = ri;
+        acc[0] += rhat[i] * ri;
+        acc[2] += ri * ri;
+    }
+    if (!grid_reduce<3>(acc, partials, &sc->ticket[1], red)) return;
+    if (threadIdx.x != 0) return;
+    const double rho_new = acc[0], rr = acc[2];
+    sc->rr = rr;
+    sc->iter += 1;
+    if (rr <= sc->tol2) { sc->done = 1; return; }
+    if (sc->iter >= sc->max_iter) { sc->done = 2; return; }
+    const double beta = (rho_new / sc->rho) * (sc->alpha / sc->omega);
+    if (!(beta == beta) || !(fabs(beta) < 1e300) || sc->omega == 0.0) { sc->breakdown = 1; sc->done = 3; return; }
+    sc->rho_old = sc->rho;
+    sc->rho = rho_new;
+    sc->beta = beta;
+}
+
+// BiCGSTAB step 5:  p = r + beta (p - omega v);  ph = dinv p
+__global__ void __launch_bounds__(RPB) bicg_p_kernel(int64_t n, const Scal *__restrict__ sc,
+                                                     const double *__restrict__ dinv,
+                                                     const double *__restrict__ r, const double *__restrict__ v,
+                                                     double *__restrict__ p, double *__restrict__ ph) {
+    if (sc->done) return;
+    const double beta = sc->beta, omega = sc->omega;
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        const double pi = r[i] + beta * (p[i] - omega * v[i]);
+        p[i] = pi;
+        ph[i] = dinv[i] * pi;
+    }
+}
+
+// BiCGSTAB start from residual r:  rhat = r; p = r; ph = dinv p; rho = r.r; rr = r.r
+__global__ void __launch_bounds__(RPB) bicg_init_kernel(int64_t n, Scal *sc, const double *__restrict__ dinv,
+                                                        const double *__restrict__ r, double *__restrict__ rhat,
+                                                        double *__restrict__ p, double *__restrict__ ph,
+                                                        double *partials) {
+    __shared__ double red[3][RPB / 32];
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        const double ri = r[i];
+        rhat[i] = ri;
+        p[i] = ri;
+        ph[i] = dinv[i] * ri;
+        acc[0] += ri * ri;
+    }
+    if (!grid_reduce<3>(acc, partials, &sc->ticket[1], red)) return;
+    if (threadIdx.x != 0) return;
+    sc->rho = acc[0];
+    sc->rho_old = acc[0];
+    sc->rr = acc[0];
+    sc->omega = 1.0;
+    sc->alpha = 1.0;
+    if (acc[0] <= sc->tol2) sc->done = 1;
+}
+
+// sum of squares (for ||b||, ||L v - r||)
+__global__ void __launch_bounds__(RPB) sumsq_kernel(int64_t n, const double *__restrict__ a,
+                                                    const double *__restrict__ b, Scal *sc, double *out,
+                                                    double *partials) {
+    // out = sum (a_i - b_i)^2   (b may be null)
+    __shared__ double red[3][RPB / 32];
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+        const double d = b ? a[i] - b[i] : a[i];
+        acc[0] += d * d;
+    }
+    if (!grid_reduce<3>(acc, partials, &sc->ticket[2], red)) return;
+    if (threadIdx.x == 0) *out = acc[0];
+}
+
+}  // namespace pdnk

@@ -1,0 +1,136 @@
+"""Host logic and the C-ABI surface -- CPU only (no compute calls)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import scipy.sparse
+
+from conftest import ROOT, golden_system_files, load_system
+from padne_b200 import capi, synth
+from padne_b200.flat import FlatSystem, KIND_REGULATOR, KIND_VOLTAGE, OP_ADD, OP_SET
+from padne_b200.stamps import build_rhs, build_stamps
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "padne_b200.h")).read()
+    declared = set(re.findall(r"\b(pdn_[a-z0-9_]+)\s*\(", header))
+    declared -= {"pdn_ctx"}          # "pdn_ctx (the reference ..." in a comment
+    assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
+    lib = capi.load_library()
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_strerror_and_struct_layout():
+    lib = capi.load_library()
+    assert lib.pdn_strerror(0) == b"ok"
+    assert b"singular" in lib.pdn_strerror(capi.PDN_ESINGULAR)
+    assert lib.pdn_strerror(capi.PDN_ENONMANIFOLD) == b"Non-manifold mesh"
+    assert ctypes.sizeof(capi.PdnOpts) == 40
+    assert ctypes.sizeof(capi.PdnInfo) == 72
+
+
+def test_no_gpu_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        capi.Context(0)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "padne_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f
+                assert "padne_oracle" not in src, f
+
+
+def test_stamp_order_and_ops():
+    z = np.zeros(1, np.int64)
+    fs = FlatSystem(v_off=z, t_off=z, xy=np.zeros((0, 2)), tri=np.zeros((0, 3), np.int32), conductance=np.zeros(0),
+                    n_internal=4, n_extra=2, i_gnd=1,
+                    e_kind=[0, 2, 3, 1], e_node=[[0, 1, 0, 0], [1, 2, 0, 0], [2, 3, 0, 1], [3, 0, 0, 0]],
+                    e_val=[2.0, 5.0, 3.3, 0.25], e_gain=[0, 0, 0.5, 0], e_xidx=[-1, 4, 5, -1])
+    s_row, s_col, s_val, s_op, r = build_stamps(fs)
+    # resistor: 4 adds; source: 4 sets; regulator: 4 sets + 2 adds; ground: 2 sets
+    assert list(s_op) == [OP_ADD] * 4 + [OP_SET] * 4 + [OP_SET] * 4 + [OP_ADD] * 2 + [OP_SET] * 2
+    assert list(zip(s_row[:4], s_col[:4])) == [(0, 0), (0, 1), (1, 1), (1, 0)]
+    assert list(s_val[:4]) == [-0.5, 0.5, -0.5, 0.5]
+    assert list(zip(s_row[4:8], s_col[4:8], s_val[4:8])) == [(4, 1, 1.0), (4, 2, -1.0), (1, 4, 1.0), (2, 4, -1.0)]
+    assert list(zip(s_row[12:14], s_col[12:14], s_val[12:14])) == [(0, 5, 0.5), (1, 5, -0.5)]
+    assert list(zip(s_row[14:], s_col[14:])) == [(6, 1), (1, 6)]
+    assert r[4] == 5.0 and r[5] == 3.3 and r[3] == 0.25 and r[0] == -0.25 and r[6] == 0.0
+
+
+@pytest.mark.parametrize("path", golden_system_files(), ids=os.path.basename)
+def test_rhs_matches_reference(path):
+    fs, d = load_system(path)
+    assert np.array_equal(build_rhs(fs), d["r"])
+
+
+def test_synth_to_flat_matches_golden_inputs():
+    # the generator is deterministic: regenerating a golden board gives the stored geometry
+    fs, d = load_system([p for p in golden_system_files() if "2layer_24" in p][0])
+    b = synth.board_2layer(24, n_via=2, size_mm=10.0, seed=2).to_flat()
+    # the reference's face iteration starts at the LAST half-edge (mesh.py:323): (v3, v1, v2)
+    assert np.array_equal(b.xy, fs.xy) and np.array_equal(np.roll(b.tri, 1, axis=1), fs.tri)
+    assert b.N == fs.N and b.n_elements == fs.n_elements
+    assert np.array_equal(b.e_kind, fs.e_kind) and np.array_equal(b.e_val, fs.e_val)
+
+
+def test_synth_sizes_of_the_baseline_configs():
+    # 2 x 708^2 = 1 002 528 grid vertices before via holes
+    b = synth.board_2layer(64, n_via=2)
+    fs = b.to_flat()
+    assert fs.n_mesh == 2 and fs.n_vertices == 2 * (64 * 64 - 4 * 9)
+    assert fs.has_regulator is False
+    r = synth.board_4layer_regulator(40, n_via=2).to_flat()
+    assert r.has_regulator and r.n_extra == 3 and int((r.e_kind == KIND_REGULATOR).sum()) == 2
+    assert int((r.e_kind == KIND_VOLTAGE).sum()) == 1
+
+
+def test_flat_system_validation():
+    with pytest.raises(ValueError):
+        FlatSystem(v_off=[0, 3], t_off=[0, 1], xy=np.zeros((2, 2)), tri=np.zeros((1, 3), np.int32), conductance=[1.0])
+
+
+def test_stamp_network_into_system_host_mirror():
+    # same writes as the reference on a lil_matrix (tests/test_solver.py:21-63 style)
+    from padne_b200 import solver as S
+
+    class NodeID:
+        pass
+
+    class Resistor:
+        def __init__(self, a, b, resistance):
+            self.a, self.b, self.resistance = a, b, resistance
+
+    class VoltageSource:
+        def __init__(self, p, n, voltage):
+            self.p, self.n, self.voltage = p, n, voltage
+
+    class Net:
+        pass
+
+    class Idx:
+        pass
+
+    a, b = NodeID(), NodeID()
+    vs = VoltageSource(b, a, 3.3)
+    net = Net()
+    net.elements = [vs, Resistor(a, b, 2.2)]
+    idx = Idx()
+    idx.node_to_global_index = {a: 0, b: 1}
+    idx.extra_source_to_global_index = {vs: 2}
+    L = scipy.sparse.lil_matrix((3, 3))
+    r = np.zeros(3)
+    S.stamp_network_into_system(net, idx, L, r)
+    g = 1 / 2.2
+    expect = np.array([[-g, g, -1.0], [g, -g, 1.0], [-1.0, 1.0, 0.0]])
+    assert np.array_equal(L.toarray(), expect)
+    assert np.array_equal(r, [0.0, 0.0, 3.3])
