@@ -136,9 +136,11 @@ int pdn_solve(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v, 
 
 /* y = L x with the resident full system (diagnostics, tests, SpMV benchmarking). x,y [N]. */
 int pdn_spmv(pdn_ctx *ctx, const double *x, double *y, int on_device);
-/* Time `reps` launches of the solver's SpMV kernel on the resident system with CUDA events on the
- * context stream; returns the mean milliseconds per launch.  flush_l2 != 0 writes a >L2 buffer
- * between launches (outside the events). */
+/* Time `reps` launches of the solver's dominant kernel (the SpMV with fused dot products, on the
+ * reduced operator of the last pdn_solve) with CUDA events on the context stream; returns the mean
+ * milliseconds per launch.  flush_l2: 0 = back-to-back (warm L2), 1 = a >L2 buffer is written
+ * before every launch (cold), 2 = in situ: each SpMV is followed by the PCG vector update like a
+ * solver iteration and only the SpMV is bracketed by the events. */
 int pdn_bench_spmv(pdn_ctx *ctx, int32_t reps, int flush_l2, double *ms_per_launch);
 
 /* ---- next row F1: per-face power density ----------------------------------------------------------

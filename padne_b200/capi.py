@@ -276,9 +276,11 @@ class Context:
         self._check(self._lib.pdn_spmv(self._ctx, _ptr(x), _ptr(y), int(dev)), "spmv")
         return y
 
-    def bench_spmv(self, reps: int = 50, flush_l2: bool = False) -> float:
+    def bench_spmv(self, reps: int = 50, mode: int = 0) -> float:
+        """Mean ms per launch of the solver's SpMV kernel; mode 0 warm L2, 1 cold L2, 2 in situ
+        (interleaved with the PCG vector update like a solver iteration)."""
         ms = ctypes.c_double()
-        self._check(self._lib.pdn_bench_spmv(self._ctx, int(reps), int(flush_l2), ctypes.byref(ms)), "bench_spmv")
+        self._check(self._lib.pdn_bench_spmv(self._ctx, int(reps), int(mode), ctypes.byref(ms)), "bench_spmv")
         return float(ms.value)
 
     # -- row F1 ---------------------------------------------------------------------------------------

@@ -285,7 +285,7 @@ int pdn_bench_spmv(pdn_ctx *ctx, int32_t reps, int flush_l2, double *ms_per_laun
     return pdn_guard(ctx, [&] {
         if (!ctx->L.valid) PDN_FAIL(PDN_ENOSYSTEM, "bench_spmv: no resident system");
         if (reps <= 0 || !ms_per_launch) PDN_FAIL(PDN_EINVAL, "bench_spmv: bad arguments");
-        pdn_bench_spmv_impl(ctx, reps, flush_l2 != 0, ms_per_launch);
+        pdn_bench_spmv_impl(ctx, reps, flush_l2, ms_per_launch);
     });
 }
 

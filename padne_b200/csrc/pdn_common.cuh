@@ -169,7 +169,7 @@ void pdn_power_density_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, const d
 void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v,
                     pdn_info *info, bool on_device);
 void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device);
-void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, bool flush_l2, double *ms);
+void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms);
 void pdn_solve_release(pdn_ctx *ctx);
 
 // SpMV launcher shared by solve / diagnostics (pdn_spmv.cu): y = A x, optional fused dot.

@@ -917,35 +917,34 @@ void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device) {
 
 // Times the kernel that dominates the solve: the CG-mode SpMV (fused r.z, z.w, r.r) on the reduced
 // operator of the last pdn_solve; falls back to the full system when no solve has run yet.
-void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, bool flush_l2, double *ms) {
+//   mode 0: back-to-back launches (warm L2)
+//   mode 1: a >L2 buffer is written before every launch (cold L2)
+//   mode 2: in situ -- every SpMV is followed by the PCG vector update, exactly like one solver
+//           iteration, and only the SpMV is bracketed by events (the cache state of the real solve)
+void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
     SolveWork *w = get_work(ctx);
     cudaStream_t st = ctx->stream;
     Operator A = w->have_operator ? w->A : full_operator(ctx, ctx->L.n);
     const int64_t n = A.n;
-    DevBuf<double> x, y, aux;
-    x.reserve((size_t)ctx->L.n);
-    y.reserve((size_t)ctx->L.n);
-    aux.reserve((size_t)ctx->L.n);
-    PDN_LAUNCH(ctx, ones_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, x.p);
-    PDN_LAUNCH(ctx, ones_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, aux.p);
-    reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);
+    DevBuf<double> x, y, aux, v3, v4, v5, v6;
+    x.reserve((size_t)n); y.reserve((size_t)n); aux.reserve((size_t)n);
+    const int vgrid = pdn_grid(ctx, n, BLK, 8);
+    PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, x.p);
+    PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, aux.p);
+    if (mode == 2) {
+        v3.reserve((size_t)n); v4.reserve((size_t)n); v5.reserve((size_t)n); v6.reserve((size_t)n);
+        PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v3.p);
+        PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v4.p);
+        PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v5.p);
+        PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v6.p);
+    }
     cudaEvent_t e0, e1;
     PDN_CUDA(cudaEventCreate(&e0));
     PDN_CUDA(cudaEventCreate(&e1));
     double total = 0.0;
+    reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);
     for (int k = 0; k < 3; k++) launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
-    if (flush_l2) {
-        for (int k = 0; k < reps; k++) {
-            pdn_flush_l2(ctx);
-            PDN_CUDA(cudaEventRecord(e0, st));
-            launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
-            PDN_CUDA(cudaEventRecord(e1, st));
-            PDN_CUDA(cudaEventSynchronize(e1));
-            float t = 0.f;
-            cudaEventElapsedTime(&t, e0, e1);
-            total += t;
-        }
-    } else {
+    if (mode < 0) {  // unbracketed back-to-back form (kept for experiments; `done` may latch)
         PDN_CUDA(cudaEventRecord(e0, st));
         for (int k = 0; k < reps; k++) launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
         PDN_CUDA(cudaEventRecord(e1, st));
@@ -953,7 +952,25 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, bool flush_l2, double *ms) 
         float t = 0.f;
         cudaEventElapsedTime(&t, e0, e1);
         total = t;
+    } else {
+        for (int k = 0; k < reps; k++) {
+            if (mode == 1) pdn_flush_l2(ctx);
+            reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);   // keeps `done` clear whatever the data does
+            PDN_CUDA(cudaEventRecord(e0, st));
+            launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
+            PDN_CUDA(cudaEventRecord(e1, st));
+            if (mode == 2) {
+                reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);
+                // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux  (alpha = beta = 0)
+                PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, n, w->d_sc, v6.p, y.p, x.p, v3.p, v4.p, v5.p, aux.p);
+            }
+            PDN_CUDA(cudaEventSynchronize(e1));
+            float t = 0.f;
+            cudaEventElapsedTime(&t, e0, e1);
+            total += t;
+        }
     }
+    PDN_CUDA(cudaStreamSynchronize(st));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     *ms = total / reps;

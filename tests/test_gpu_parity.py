@@ -194,8 +194,10 @@ def test_solve_matches_spsolve(ctx, name, board):
     v_ref, res_ref, ig_ref = oracle.solve(indptr, indices, data, rhs)      # the reference's own spsolve call
     assert info.rel_residual <= RESIDUAL_RTOL
     assert voltage_error(v, v_ref, fs.n_nodes) <= VOLTAGE_RTOL
-    assert np.allclose(v[fs.n_nodes:], v_ref[fs.n_nodes:], rtol=1e-5, atol=1e-7)
-    assert abs(info.ground_node_current - ig_ref) < 1e-7
+    # currents are recovered from node residuals: their absolute accuracy scales with the largest current
+    i_scale = max(1.0, np.max(np.abs(v_ref[fs.n_nodes:])))
+    assert np.allclose(v[fs.n_nodes:], v_ref[fs.n_nodes:], rtol=1e-5, atol=1e-7 * i_scale)
+    assert abs(info.ground_node_current - ig_ref) < 1e-7 * i_scale
 
 
 def test_solve_autodetects_n_nodes_and_accepts_foreign_csr(ctx):
