@@ -4,12 +4,7 @@
 // Replaces scipy.sparse.linalg.spsolve at padne/solver.py:772-775 (SuperLU) by an iterative solve;
 // the operator is the reduced system  A = -(Z^T Q L Z)  described in pdn_solve.cu.
 //
-// SpMV layout ("CSR-stream"): a block owns RPB consecutive rows.  Their stored entries are one
-// contiguous range of the CSR arrays, so the block streams values (8 B) and column indices (4 B)
-// with fully coalesced loads, multiplies by the gathered x (read-only path, L1/L2 resident for
-// mesh-local numbering) into shared memory, and each thread then sums its own row out of shared
-// memory in column order.  HBM traffic is the algorithmic 12 B/nnz + 4 B/row + vectors, there is
-// no padding and no row permutation, and the per-row summation order is fixed (bit-reproducible).
+// The SpMV (pdn_spmv.cuh) streams the CSR arrays through a TMA bulk-copy pipeline.
 //
 // Dot products are fused into the kernel that produces their operands.  Every block writes one
 // partial per accumulator; the LAST block to finish (ticket counter) adds the partials in a
@@ -20,8 +15,7 @@
 
 namespace pdnk {
 
-constexpr int RPB = 256;       // rows (= threads) per block
-constexpr int CAP = 2560;      // products staged per chunk (20 KB of shared memory)
+constexpr int RPB = 256;       // threads per block of the vector kernels
 constexpr int MAX_PART = 2048; // upper bound on blocks that write reduction partials
 
 // device-resident scalars of one Krylov solve
@@ -56,8 +50,8 @@ struct Operator {
 
 __device__ __forceinline__ int32_t rp_decode(int32_t v) { return v < 0 ? ~v : v; }
 
-template <int NACC>
-__device__ __forceinline__ void block_reduce(double (&acc)[NACC], double (*sm)[RPB / 32]) {
+template <int NACC, int NW = RPB / 32>
+__device__ __forceinline__ void block_reduce(double (&acc)[NACC], double (*sm)[NW]) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int a = 0; a < NACC; a++) {
@@ -69,7 +63,7 @@ __device__ __forceinline__ void block_reduce(double (&acc)[NACC], double (*sm)[R
     if (warp == 0) {
 #pragma unroll
         for (int a = 0; a < NACC; a++) {
-            double v = lane < RPB / 32 ? sm[a][lane] : 0.0;
+            double v = lane < NW ? sm[a][lane] : 0.0;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
             acc[a] = v;  // valid in thread 0
@@ -80,11 +74,11 @@ __device__ __forceinline__ void block_reduce(double (&acc)[NACC], double (*sm)[R
 
 // Write this block's partials; returns true (to all threads) in the last block to arrive, with
 // acc[] holding the grid totals summed in block order.
-template <int NACC>
+template <int NACC, int NW = RPB / 32>
 __device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partials, unsigned int *ticket,
-                                            double (*sm)[RPB / 32]) {
+                                            double (*sm)[NW]) {
     __shared__ bool is_last;
-    block_reduce<NACC>(acc, sm);
+    block_reduce<NACC, NW>(acc, sm);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int a = 0; a < NACC; a++) partials[a * MAX_PART + blockIdx.x] = acc[a];
@@ -98,137 +92,23 @@ __device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partial
 #pragma unroll
     for (int a = 0; a < NACC; a++) {
         double v = 0.0;
-        for (int b = threadIdx.x; b < (int)gridDim.x; b += RPB) v += __ldcg(&partials[a * MAX_PART + b]);
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += NW * 32) v += __ldcg(&partials[a * MAX_PART + b]);
         acc[a] = v;
     }
-    block_reduce<NACC>(acc, sm);
+    block_reduce<NACC, NW>(acc, sm);
     if (threadIdx.x == 0) *ticket = 0u;
     return true;
 }
 
 // ------------------------------------------------------------------------------------------------
-// SpMV with fused dots
+// SpMV with fused dots (TMA-pipelined CSR-stream kernel)
 //   PLAIN : y = A x
 //   CG    : y = A x (x = z);   gamma = r.z, delta = z.y, rr = r.r        aux0 = r
 //   BICG_V: y = A x (x = ph);  r0v = rhat.y                               aux0 = rhat
 //   BICG_T: y = A x (x = sh);  ts = y.s, tt = y.y                         aux0 = s
 //   RESID : y = b - A x;       rr = y.y                                   aux0 = b
 // ------------------------------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(RPB) spmv_kernel(Operator A, const double *__restrict__ x,
-                                                   double *__restrict__ y, const double *__restrict__ aux0,
-                                                   Scal *sc, double *partials) {
-    __shared__ double prod[CAP];
-    __shared__ double red[3][RPB / 32];
-    if (MODE != PLAIN && MODE != RESID) {
-        if (sc->done) return;
-    }
-    double acc[3] = {0.0, 0.0, 0.0};
-    const int64_t n_blk = (A.n + RPB - 1) / RPB;
-    for (int64_t blk = blockIdx.x; blk < n_blk; blk += gridDim.x) {
-        const int64_t r0 = blk * RPB;
-        const int64_t r1 = r0 + RPB < A.n ? r0 + RPB : A.n;
-        const int64_t row = r0 + threadIdx.x;
-        int32_t lo = 0, hi = 0;
-        bool special = true;
-        if (row < r1) {
-            const int32_t v = A.rp[row];
-            special = v < 0;
-            lo = rp_decode(v);
-            hi = special ? lo : rp_decode(A.rp[row + 1]);
-        }
-        const int32_t k0 = rp_decode(A.rp[r0]), k1 = rp_decode(A.rp[r1]);
-        double sum = 0.0;
-        for (int32_t c0 = k0; c0 < k1; c0 += CAP) {
-            const int32_t c1 = c0 + CAP < k1 ? c0 + CAP : k1;
-#pragma unroll 4
-            for (int32_t k = c0 + threadIdx.x; k < c1; k += RPB)
-                prod[k - c0] = A.va[k] * __ldg(&x[A.ci[k]]);
-            __syncthreads();
-            const int32_t a = lo > c0 ? lo : c0, b = hi < c1 ? hi : c1;
-            for (int32_t k = a; k < b; k++) sum += prod[k - c0];
-            __syncthreads();
-        }
-        if (row < r1 && !special) {
-            if (MODE == PLAIN) {
-                y[row] = sum;
-            } else if (MODE == CG) {
-                const double zi = x[row], ri = aux0[row];
-                y[row] = sum;
-                acc[0] += ri * zi; acc[1] += zi * sum; acc[2] += ri * ri;
-            } else if (MODE == BICG_V) {
-                y[row] = sum;
-                acc[0] += aux0[row] * sum;
-            } else if (MODE == BICG_T) {
-                y[row] = sum;
-                acc[0] += sum * aux0[row]; acc[1] += sum * sum;
-            } else {  // RESID
-                const double ri = aux0[row] - sum;
-                y[row] = ri;
-                acc[2] += ri * ri;
-            }
-        }
-    }
-    // override rows (constraint terminals): block 0, one thread per row
-    if (blockIdx.x == 0) {
-        for (int32_t t = threadIdx.x; t < A.n_special; t += RPB) {
-            const int32_t row = A.sp_row[t];
-            double sum = 0.0;
-            for (int32_t k = A.sp_rp[t]; k < A.sp_rp[t + 1]; k++) sum += A.sp_va[k] * x[A.sp_ci[k]];
-            if (MODE == PLAIN) {
-                y[row] = sum;
-            } else if (MODE == CG) {
-                const double zi = x[row], ri = aux0[row];
-                y[row] = sum;
-                acc[0] += ri * zi; acc[1] += zi * sum; acc[2] += ri * ri;
-            } else if (MODE == BICG_V) {
-                y[row] = sum;
-                acc[0] += aux0[row] * sum;
-            } else if (MODE == BICG_T) {
-                y[row] = sum;
-                acc[0] += sum * aux0[row]; acc[1] += sum * sum;
-            } else {
-                const double ri = aux0[row] - sum;
-                y[row] = ri;
-                acc[2] += ri * ri;
-            }
-        }
-    }
-    if (MODE == PLAIN) return;
-    if (!grid_reduce<3>(acc, partials, &sc->ticket[0], red)) return;
-    if (threadIdx.x != 0) return;
-    if (MODE == CG) {
-        const double gamma = acc[0], delta = acc[1], rr = acc[2];
-        sc->rr = rr;
-        if (rr <= sc->tol2) { sc->done = 1; return; }
-        if (sc->iter >= sc->max_iter) { sc->done = 2; return; }
-        double beta, alpha;
-        if (sc->first) {
-            beta = 0.0;
-            alpha = gamma / delta;
-            sc->first = 0;
-        } else {
-            beta = gamma / sc->gamma_old;
-            alpha = gamma / (delta - beta * gamma / sc->alpha);
-        }
-        if (!(alpha == alpha) || !(fabs(alpha) < 1e300) || delta <= 0.0) { sc->breakdown = 1; sc->done = 3; return; }
-        sc->gamma_old = gamma;
-        sc->gamma = gamma; sc->delta = delta;
-        sc->alpha = alpha; sc->beta = beta;
-        sc->iter += 1;
-    } else if (MODE == BICG_V) {
-        sc->r0v = acc[0];
-        const double alpha = sc->rho / acc[0];
-        if (!(alpha == alpha) || !(fabs(alpha) < 1e300)) { sc->breakdown = 1; sc->done = 3; return; }
-        sc->alpha = alpha;
-    } else if (MODE == BICG_T) {
-        sc->ts = acc[0]; sc->tt = acc[1];
-        const double omega = acc[1] > 0.0 ? acc[0] / acc[1] : 0.0;
-        sc->omega = omega;
-    } else if (MODE == RESID) {
-        sc->rr = acc[2];
-    }
-}
+#include "pdn_spmv.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // fused vector kernels (grid-stride, one element per thread per step)

@@ -198,8 +198,10 @@ static SolveWork *get_work(pdn_ctx *ctx) {
 }
 
 static int spmv_grid(const pdn_ctx *ctx, int64_t n) {
-    int64_t nb = (n + RPB - 1) / RPB;
-    int64_t full = (int64_t)ctx->n_sm * 8;
+    int64_t nb = (n + SROWS - 1) / SROWS;
+    int per_sm = (int)((227 * 1024) / (SPMV_SMEM + 1024));
+    if (per_sm > 8) per_sm = 8;
+    int64_t full = (int64_t)ctx->n_sm * per_sm;
     if (full > MAX_PART) full = MAX_PART;
     if (nb < 1) nb = 1;
     return (int)(nb < full ? nb : full);
@@ -218,7 +220,12 @@ static Operator full_operator(const pdn_ctx *ctx, int64_t rows) {
 template <int MODE>
 static void launch_spmv(pdn_ctx *ctx, const Operator &A, const double *x, double *y, const double *aux,
                         SolveWork *w) {
-    PDN_LAUNCH(ctx, spmv_kernel<MODE>, spmv_grid(ctx, A.n), RPB, 0, A, x, y, aux, w->d_sc, w->partials.p);
+    static bool configured = false;
+    if (!configured) {
+        PDN_CUDA(cudaFuncSetAttribute(spmv_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SPMV_SMEM));
+        configured = true;
+    }
+    PDN_LAUNCH(ctx, spmv_kernel<MODE>, spmv_grid(ctx, A.n), STHREADS, SPMV_SMEM, A, x, y, aux, w->d_sc, w->partials.p);
 }
 
 static void fetch_scal(pdn_ctx *ctx, SolveWork *w) {
