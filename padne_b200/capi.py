@@ -72,7 +72,7 @@ def load_library(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("PADNE_B200_LIB") or LIB_PATH
     if not os.path.exists(p):
         raise RuntimeError(f"{p} is missing: run `python -m padne_b200.build` (there is no CPU fallback)")
     lib = ctypes.CDLL(p)

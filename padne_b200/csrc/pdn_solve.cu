@@ -945,40 +945,28 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
         PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v5.p);
         PDN_LAUNCH(ctx, ones_kernel, vgrid, BLK, 0, n, v6.p);
     }
-    cudaEvent_t e0, e1;
-    PDN_CUDA(cudaEventCreate(&e0));
-    PDN_CUDA(cudaEventCreate(&e1));
-    double total = 0.0;
-    reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);
+    // max_iter < 0 tells the kernel's scalar epilogue to leave `done` alone (benchmark mode), so all
+    // launches can be queued back to back; every SpMV gets its own event pair and the host
+    // synchronises once at the end, like the kernels inside the solver's CUDA graph.
+    reset_scal(ctx, w, 0.0, 0.0, -1);
     for (int k = 0; k < 3; k++) launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
-    if (mode < 0) {  // unbracketed back-to-back form (kept for experiments; `done` may latch)
-        PDN_CUDA(cudaEventRecord(e0, st));
-        for (int k = 0; k < reps; k++) launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
-        PDN_CUDA(cudaEventRecord(e1, st));
-        PDN_CUDA(cudaEventSynchronize(e1));
-        float t = 0.f;
-        cudaEventElapsedTime(&t, e0, e1);
-        total = t;
-    } else {
-        for (int k = 0; k < reps; k++) {
-            if (mode == 1) pdn_flush_l2(ctx);
-            reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);   // keeps `done` clear whatever the data does
-            PDN_CUDA(cudaEventRecord(e0, st));
-            launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
-            PDN_CUDA(cudaEventRecord(e1, st));
-            if (mode == 2) {
-                reset_scal(ctx, w, 0.0, 0.0, 0x7fffffff);
-                // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux  (alpha = beta = 0)
-                PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, n, w->d_sc, v6.p, y.p, x.p, v3.p, v4.p, v5.p, aux.p);
-            }
-            PDN_CUDA(cudaEventSynchronize(e1));
-            float t = 0.f;
-            cudaEventElapsedTime(&t, e0, e1);
-            total += t;
-        }
+    std::vector<cudaEvent_t> ev(2 * (size_t)reps);
+    for (auto &e : ev) PDN_CUDA(cudaEventCreate(&e));
+    for (int k = 0; k < reps; k++) {
+        if (mode == 1) pdn_flush_l2(ctx);
+        PDN_CUDA(cudaEventRecord(ev[2 * k], st));
+        launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
+        PDN_CUDA(cudaEventRecord(ev[2 * k + 1], st));
+        if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
+            PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, n, w->d_sc, v6.p, y.p, x.p, v3.p, v4.p, v5.p, aux.p);
     }
     PDN_CUDA(cudaStreamSynchronize(st));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
+    double total = 0.0;
+    for (int k = 0; k < reps; k++) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, ev[2 * k], ev[2 * k + 1]);
+        total += t;
+    }
+    for (auto &e : ev) cudaEventDestroy(e);
     *ms = total / reps;
 }

@@ -227,6 +227,18 @@ def test_solve_not_converged_is_loud(ctx):
         ctx.solve(rhs, n_nodes=fs.n_nodes, max_iter=5)
 
 
+def test_solve_multi_item_pipeline_matches_spsolve(ctx):
+    # > 592 CTAs x 128 rows: every CTA streams several work items through the TMA pipeline
+    fs = synth.board_2layer(300, n_via=6, size_mm=40.0, seed=13).to_flat()
+    indptr, indices, data, rhs = gpu_assemble(ctx, fs)
+    v, info = ctx.solve(rhs, n_nodes=fs.n_nodes)
+    v_ref, _, _ = oracle.solve(indptr, indices, data, rhs)
+    assert info.rel_residual <= RESIDUAL_RTOL
+    assert voltage_error(v, v_ref, fs.n_nodes) <= VOLTAGE_RTOL
+    v2, info2 = ctx.solve(rhs, n_nodes=fs.n_nodes)
+    assert np.array_equal(v, v2) and info.iterations == info2.iterations
+
+
 def test_solve_is_deterministic(ctx):
     fs = synth.board_2layer(100, n_via=3, size_mm=20.0, seed=7).to_flat()
     _, _, _, rhs = gpu_assemble(ctx, fs)
@@ -235,8 +247,9 @@ def test_solve_is_deterministic(ctx):
     assert np.array_equal(v1, v2) and i1.iterations == i2.iterations
 
 
-def test_spmv_matches_scipy(ctx):
-    fs = synth.board_8layer(50, n_via=2, size_mm=30.0, seed=4).to_flat()
+@pytest.mark.parametrize("grid", [50, 180])       # 180: several work items per CTA (pipelined path)
+def test_spmv_matches_scipy(ctx, grid):
+    fs = synth.board_8layer(grid, n_via=2, size_mm=30.0, seed=4).to_flat()
     indptr, indices, data, _ = gpu_assemble(ctx, fs)
     L = scipy.sparse.csr_matrix((data, indices, indptr), shape=(fs.N, fs.N))
     x = np.random.default_rng(0).standard_normal(fs.N)
