@@ -16,8 +16,13 @@ BASELINE.json configs[1] (2-layer 100x100 mm plane, ~1M DOF, one VOLTAGE + one C
   cpu_baseline  the oracle port (C assembly restatement + the reference's own scipy spsolve call)
              on a bounded sample of the same board family, 1 core
 
-Multi-GPU (torchrun, one rank per GPU): every rank assembles and solves its own board of the
-configured size (boards are independent objects: no data-path collective), "scaling": "weak".
+Multi-GPU (torchrun, one rank per GPU), --multi partitioned (default): ONE board is partitioned across
+the ranks -- contiguous row ranges of the reduced system, NCCL halo exchange of the interface entries
+before every SpMV and an all-reduce of the fused dot products (csrc/pdn_multi.cu).  Without --config the
+board grows with the job, 2 layers of 708x708 (~1M DOF) per GPU, "scaling": "weak"; with an explicit
+--config (e.g. 8layer_10M) that fixed board is split, "scaling": "strong".  DOFs are counted once per
+step (not once per rank).  --multi independent runs one independent 2layer_1M board per rank instead
+(no data-path collective).
 """
 from __future__ import annotations
 
@@ -58,6 +63,9 @@ def measured_peak_gbs():
 
 def make_board(config: str, n: int | None):
     from padne_b200 import synth
+    if config.startswith("stack_"):          # stack_<L>layer: the weak-scaling family, L planes of n x n
+        layers = int(config.split("_")[1].replace("layer", ""))
+        return synth.board_8layer(n or 708, n_via=16 if (n or 708) >= 200 else 2, size_mm=100.0, n_layers=layers)
     if config == "2layer_1M":
         return synth.board_2layer(n or 708, n_via=16 if (n or 708) >= 200 else 2)
     if config == "4layer_regulator_4M":
@@ -150,7 +158,7 @@ def run_reference(args, rank, world):
               f"slower than this port")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.config, "grid": n_sample, "dof": N},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -162,7 +170,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--config", default="2layer_1M")
+    ap.add_argument("--config", default=None, help="default: 2layer_1M at 1 GPU, stack_<2N>layer at N GPUs")
+    ap.add_argument("--multi", default="partitioned", choices=["partitioned", "independent"])
     ap.add_argument("--n", type=int, default=None, help="grid vertices per side (default: the config's full size)")
     ap.add_argument("--impl", default="padne_b200", choices=["padne_b200", "reference"])
     ap.add_argument("--cpu-sample-n", type=int, default=260, help="grid size of the CPU-baseline sample")
@@ -174,6 +183,17 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    partitioned = world > 1 and args.multi == "partitioned"
+    scaling = "weak"
+    if args.config is None:
+        args.config = f"stack_{2 * world}layer" if partitioned else "2layer_1M"
+    elif partitioned:
+        scaling = "strong"
+    args.scaling = scaling
+    if args.config.startswith("stack_") and args.n is None:
+        # keep the bounded CPU sample at ~130k DOF whatever the number of layers
+        layers = int(args.config.split("_")[1].replace("layer", ""))
+        args.cpu_sample_n = max(40, int(args.cpu_sample_n * (2.0 / layers) ** 0.5))
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -213,6 +233,9 @@ def main():
 
     ctx = capi.Context(local_rank)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    if partitioned:
+        from padne_b200 import dist as pdist
+        pdist.init_comm(ctx)                # every pdn_solve below is a collective over all ranks
 
     def step_device():
         nnz = ctx.assemble(devt["v_off"], devt["xy"], devt["t_off"], devt["tri"], devt["cond"], fs.N,
@@ -263,6 +286,8 @@ def main():
     nnz_nodes = int(indptr_tail[n_red])
     del indptr_tail
     alg_bytes = 12.0 * nnz_nodes + 20.0 * n_red          # 12 B/nnz + 20 B/row
+    if partitioned:
+        alg_bytes /= world                               # the timed launch covers this rank's rows only
     spmv_ms = ctx.bench_spmv(reps=200, mode=2)
     spmv_ms_warm = ctx.bench_spmv(reps=200, mode=0)
     spmv_ms_cold = ctx.bench_spmv(reps=50, mode=1)
@@ -274,25 +299,28 @@ def main():
             dist.destroy_process_group()
         return
 
-    dofs_total = fs.N * args.steps * world
+    dofs_total = fs.N * args.steps * (1 if partitioned else world)
     value = dofs_total / (t_dev_ms * 1e-3)
     e2e_value = dofs_total / (t_e2e_ms * 1e-3)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_dev_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.config, "grid": args.n or "full", "dof_per_gpu": fs.N, "nnz": int(nnz),
+        "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.config, "grid": args.n or "full", "dof": fs.N,
+                   "dof_per_gpu": fs.N // world if partitioned else fs.N, "nnz": int(nnz),
                    "layers": fs.n_mesh, "elements": fs.n_elements, "method": info.method,
                    "preconditioner": "jacobi", "iterations": info.iterations, "rtol": args.rtol,
                    "rel_residual": info.rel_residual, "residual_norm": info.residual_norm,
                    "t_krylov_ms": info.t_krylov_ms, "t_setup_ms": info.t_setup_ms,
-                   "parallelism": f"{world} independent board(s), one per GPU" if world > 1 else "single GPU",
+                   "parallelism": ("single GPU" if world == 1 else
+                                   f"one board row-partitioned over {world} GPUs (NCCL halo exchange + dot all-reduce; "
+                                   f"assembly replicated)" if partitioned else f"{world} independent boards, one per GPU"),
                    "l2": "256 MiB written between timed steps; per-step working set exceeds the 126 MB L2"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": t_e2e_ms / args.steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "pdnk::spmv_kernel<CG> (CSR-stream SpMV + fused r.z, z.w, r.r)",
+        "roofline": {"bound": "hbm", "kernel": "pdnk::sell_spmv_kernel<CG> (SELL-32-sigma SpMV + fused r.z, z.w, r.r)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                      "ms_per_launch_in_situ": spmv_ms, "ms_per_launch_warm_l2": spmv_ms_warm,

@@ -53,7 +53,7 @@ extern "C" {
 /* preconditioners */
 #define PDN_PRECOND_JACOBI 0
 #define PDN_PRECOND_NONE 1
-#define PDN_PRECOND_AMG 2     /* aggregation multigrid V-cycle with Jacobi smoothing              */
+#define PDN_PRECOND_AMG 2     /* reserved (aggregation multigrid); pdn_solve answers PDN_EUNSUPPORTED */
 
 typedef struct pdn_ctx pdn_ctx;
 
@@ -83,7 +83,9 @@ typedef struct pdn_info {
 } pdn_info;
 
 /* ---- context ------------------------------------------------------------------------------- */
-/* One context = one GPU, one stream, one resident system.  `device` is the CUDA ordinal. */
+/* One context = one GPU, one stream, one resident system.  `device` is the CUDA ordinal.
+ * Scratch buffers are kept inside the context and only grow, so repeated calls on same-sized
+ * boards allocate nothing. */
 int pdn_create(pdn_ctx **out, int device);
 int pdn_destroy(pdn_ctx *ctx);
 const char *pdn_strerror(int status);
@@ -136,12 +138,27 @@ int pdn_solve(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v, 
 
 /* y = L x with the resident full system (diagnostics, tests, SpMV benchmarking). x,y [N]. */
 int pdn_spmv(pdn_ctx *ctx, const double *x, double *y, int on_device);
-/* Time `reps` launches of the solver's dominant kernel (the SpMV with fused dot products, on the
- * reduced operator of the last pdn_solve) with CUDA events on the context stream; returns the mean
+/* Time `reps` launches of the solver's dominant kernel (the SELL-32-sigma SpMV with fused dot
+ * products, on the reduced operator of the last pdn_solve) with CUDA events on the context stream; returns the mean
  * milliseconds per launch.  flush_l2: 0 = back-to-back (warm L2), 1 = a >L2 buffer is written
  * before every launch (cold), 2 = in situ: each SpMV is followed by the PCG vector update like a
  * solver iteration and only the SpMV is bracketed by the events. */
 int pdn_bench_spmv(pdn_ctx *ctx, int32_t reps, int flush_l2, double *ms_per_launch);
+
+/* ---- multi-GPU: one process per GPU, NCCL over NVLink / NVSwitch -----------------------------------
+ * No reference equivalent (the reference is single-threaded CPU code); this is the north star's
+ * "large boards are partitioned across the GPUs of one box".  After pdn_comm_init every pdn_solve on
+ * this context is COLLECTIVE: all ranks must call it with the same resident system and the same
+ * right-hand side.  The reduced system's rows are split into contiguous ranges (whole 1024-row sort
+ * windows), each rank iterates on its own rows, exchanges the interface entries of the SpMV input
+ * with the ranks that need them (grouped ncclSend/ncclRecv) and all-reduces the fused dot products;
+ * every rank returns the full v.
+ *   pdn_comm_unique_id: call on rank 0, ship the 128 bytes to the other ranks (any transport);
+ *   pdn_comm_init:      collective; world == 1 leaves the context in single-GPU mode. */
+int pdn_comm_unique_id(void *out128);
+int pdn_comm_init(pdn_ctx *ctx, int rank, int world, const void *id128);
+int pdn_comm_destroy(pdn_ctx *ctx);
+int pdn_comm_info(pdn_ctx *ctx, int *rank, int *world);
 
 /* ---- next row F1: per-face power density ----------------------------------------------------------
  * Replaces compute_power_density / compute_triangle_gradient (padne/solver.py:689-745):

@@ -48,16 +48,24 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, defines: list[str] | None = None, tag: str | None = None) -> str:
+    """Build the library.  ``defines`` / ``tag`` build a tuning variant ``libpadne_b200_<tag>.so``
+    (kernel experiments: select it with the ``PADNE_B200_LIB`` environment variable)."""
+    if tag:
+        return _build(os.path.join(LIBDIR, f"libpadne_b200_{tag}.so"), verbose, [f"-D{d}" for d in (defines or [])], tag)
     if not force and not needs_build():
         return LIB
+    return _build(LIB, verbose, [], "")
+
+
+def _build(LIB: str, verbose: bool, extra: list[str], tag: str) -> str:
     os.makedirs(LIBDIR, exist_ok=True)
     nvcc = _nvcc()
     objs = []
     procs = []
     for unit in _sources():
-        obj = os.path.join(LIBDIR, unit.replace(".cu", ".o"))
-        cmd = [nvcc, *ARCH, *COMMON, *UNITS[unit], "-c", os.path.join(CSRC, unit), "-o", obj]
+        obj = os.path.join(LIBDIR, unit.replace(".cu", f"{tag}.o"))
+        cmd = [nvcc, *ARCH, *COMMON, *UNITS[unit], *extra, "-c", os.path.join(CSRC, unit), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd))
@@ -79,4 +87,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    # python -m padne_b200.build [--force] [-v] [--tag NAME -DFOO=1 ...]
+    tag = sys.argv[sys.argv.index("--tag") + 1] if "--tag" in sys.argv else None
+    defs = [a[2:] for a in sys.argv if a.startswith("-D")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, defines=defs, tag=tag))

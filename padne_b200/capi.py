@@ -25,7 +25,8 @@ METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 # every symbol include/padne_b200.h declares (tests check that the library exports them all)
 SYMBOLS = ("pdn_create", "pdn_destroy", "pdn_strerror", "pdn_last_error", "pdn_launch_count",
            "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_get_csr", "pdn_get_shape",
-           "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density")
+           "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density",
+           "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info")
 
 
 class SingularSystemError(RuntimeError):
@@ -96,9 +97,10 @@ def load_library(path: str | None = None):
     lib.pdn_spmv.argtypes = [P, P, P, ctypes.c_int]
     lib.pdn_bench_spmv.argtypes = [P, I32, ctypes.c_int, ctypes.POINTER(D)]
     lib.pdn_power_density.argtypes = [P, I64, P, P, I64, P, D, P, ctypes.c_int]
-    if hasattr(lib, "pdn_comm_init"):
-        lib.pdn_comm_init.argtypes = [P, ctypes.c_int, ctypes.c_int, P]
-        lib.pdn_comm_destroy.argtypes = [P]
+    lib.pdn_comm_unique_id.argtypes = [P]
+    lib.pdn_comm_init.argtypes = [P, ctypes.c_int, ctypes.c_int, P]
+    lib.pdn_comm_destroy.argtypes = [P]
+    lib.pdn_comm_info.argtypes = [P, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
     if path is None:
         _lib = lib
     return lib
@@ -183,6 +185,34 @@ class Context:
     @property
     def stream(self) -> int:
         return int(self._lib.pdn_stream(self._ctx))
+
+    # -- multi-GPU ---------------------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """128-byte NCCL id (call on rank 0 and ship it to the other ranks)."""
+        lib = load_library()
+        buf = ctypes.create_string_buffer(128)
+        st = lib.pdn_comm_unique_id(buf)
+        if st != PDN_OK:
+            raise RuntimeError(f"pdn_comm_unique_id: {lib.pdn_strerror(st).decode()}")
+        return buf.raw
+
+    def comm_init(self, rank: int, world: int, unique_id: bytes):
+        """Collective: afterwards every :meth:`solve` on this context is a collective over ``world`` ranks."""
+        if len(unique_id) != 128:
+            raise ValueError("unique_id must be the 128 bytes of comm_unique_id()")
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128)
+        self._check(self._lib.pdn_comm_init(self._ctx, int(rank), int(world), buf), "comm_init")
+
+    def comm_destroy(self):
+        self._check(self._lib.pdn_comm_destroy(self._ctx), "comm_destroy")
+
+    @property
+    def comm(self):
+        """``(rank, world)`` of this context (``(0, 1)`` without a communicator)."""
+        r, w = ctypes.c_int(), ctypes.c_int()
+        self._lib.pdn_comm_info(self._ctx, ctypes.byref(r), ctypes.byref(w))
+        return int(r.value), int(w.value)
 
     # -- kernel (1) ------------------------------------------------------------------------------
     def element_weights(self, xy, tri):

@@ -108,21 +108,21 @@ template <typename T>
 static void exclusive_scan_impl(pdn_ctx *ctx, const int32_t *in, int64_t n, T *out, DevBuf<T> &tmp) {
     int64_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (n_tiles < 1) n_tiles = 1;
-    tmp.reserve((size_t)n_tiles + 1);
+    if ((size_t)n_tiles + 1 > tmp.cap) {
+        PDN_CUDA(cudaStreamSynchronize(ctx->stream));   // an earlier scan may still read the old buffer
+        tmp.reserve((size_t)n_tiles + 1);
+    }
     PDN_LAUNCH(ctx, scan_tile_totals<T>, (int)n_tiles, SCAN_BLOCK, 0, in, n, tmp.p);
     PDN_LAUNCH(ctx, scan_totals_inplace<T>, 1, SCAN_BLOCK, 0, tmp.p, n_tiles, out + n);
     PDN_LAUNCH(ctx, scan_apply<T>, (int)n_tiles, SCAN_BLOCK, 0, in, n, tmp.p, out);
 }
 
+// the tile-total scratch lives in the context (stream-ordered reuse: no synchronisation needed)
 void pdn_exclusive_scan_i32(pdn_ctx *ctx, const int32_t *in, int64_t n, int32_t *out) {
-    DevBuf<int32_t> tmp;
-    exclusive_scan_impl<int32_t>(ctx, in, n, out, tmp);
-    PDN_CUDA(cudaStreamSynchronize(ctx->stream));  // tmp is freed on return
+    exclusive_scan_impl<int32_t>(ctx, in, n, out, ctx->scan_tmp32);
 }
 void pdn_exclusive_scan_i64(pdn_ctx *ctx, const int32_t *in, int64_t n, int64_t *out) {
-    DevBuf<int64_t> tmp;
-    exclusive_scan_impl<int64_t>(ctx, in, n, out, tmp);
-    PDN_CUDA(cudaStreamSynchronize(ctx->stream));
+    exclusive_scan_impl<int64_t>(ctx, in, n, out, ctx->scan_tmp64);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -185,6 +185,10 @@ int pdn_destroy(pdn_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     pdn_solve_release(ctx);
+    pdn_assemble_release(ctx);
+    pdn_comm_release(ctx);
+    ctx->scan_tmp32.release();
+    ctx->scan_tmp64.release();
     if (ctx->d_status) cudaFree(ctx->d_status);
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     ctx->L.indptr.release();

@@ -430,6 +430,19 @@ void pdn_power_density_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, const d
     raise_device_status(ctx, "power_density");
 }
 
+struct AssembleWork {
+    DevIn<int64_t> d_voff, d_toff;
+    DevIn<double> d_xy, d_cond, d_sval;
+    DevIn<int32_t> d_tri, d_srow, d_scol, d_sop;
+    DevBuf<double> w, tval;
+    DevBuf<int32_t> gtri, cnt, cnt_s, ub, inc_ptr, sinc_ptr, ub_ptr, inc, sinc, tcol, row_len;
+};
+
+void pdn_assemble_release(pdn_ctx *ctx) {
+    delete ctx->asmw;
+    ctx->asmw = nullptr;
+}
+
 void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
                        const int64_t *t_off, const int32_t *tri, const double *conductance, int64_t N,
                        int64_t n_stamp, const int32_t *s_row, const int32_t *s_col, const double *s_val,
@@ -455,9 +468,13 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     if (N >= 0x7fffffffLL || 3 * n_t + 2 * n_v + n_stamp >= 0x7fffffffLL)
         PDN_FAIL(PDN_EUNSUPPORTED, "assemble: system exceeds int32 indexing");
 
-    DevIn<int64_t> d_voff, d_toff;
-    DevIn<double> d_xy, d_cond, d_sval;
-    DevIn<int32_t> d_tri, d_srow, d_scol, d_sop;
+    // scratch and staging buffers live in the context and only ever grow: repeated assemblies of
+    // same-sized boards do no cudaMalloc / cudaFree at all
+    if (!ctx->asmw) ctx->asmw = new AssembleWork();
+    AssembleWork &aw = *ctx->asmw;
+    DevIn<int64_t> &d_voff = aw.d_voff, &d_toff = aw.d_toff;
+    DevIn<double> &d_xy = aw.d_xy, &d_cond = aw.d_cond, &d_sval = aw.d_sval;
+    DevIn<int32_t> &d_tri = aw.d_tri, &d_srow = aw.d_srow, &d_scol = aw.d_scol, &d_sop = aw.d_sop;
     d_voff.set(v_off, n_mesh + 1, on_device, st);
     d_toff.set(t_off, n_mesh + 1, on_device, st);
     d_xy.set(xy, (size_t)n_v * 2, on_device, st);
@@ -468,8 +485,10 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     d_sval.set(s_val, n_stamp, on_device, st);
     d_sop.set(s_op, n_stamp, on_device, st);
 
-    DevBuf<double> w, tval;
-    DevBuf<int32_t> gtri, cnt, cnt_s, ub, inc_ptr, sinc_ptr, ub_ptr, inc, sinc, tcol, row_len;
+    DevBuf<double> &w = aw.w, &tval = aw.tval;
+    DevBuf<int32_t> &gtri = aw.gtri, &cnt = aw.cnt, &cnt_s = aw.cnt_s, &ub = aw.ub, &inc_ptr = aw.inc_ptr,
+                    &sinc_ptr = aw.sinc_ptr, &ub_ptr = aw.ub_ptr, &inc = aw.inc, &sinc = aw.sinc, &tcol = aw.tcol,
+                    &row_len = aw.row_len;
     w.reserve((size_t)n_t * 3 + 1);
     gtri.reserve((size_t)n_t * 3 + 1);
     cnt.reserve((size_t)N);

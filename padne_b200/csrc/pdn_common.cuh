@@ -93,7 +93,9 @@ struct CsrDev {
     bool valid = false;
 };
 
-struct SolveWork;  // pdn_solve.cu
+struct SolveWork;     // pdn_solve.cu
+struct AssembleWork;  // pdn_assemble.cu (scratch buffers kept between calls)
+struct PdnComm;       // pdn_multi.cu
 
 struct pdn_ctx {
     int device = 0;
@@ -106,6 +108,10 @@ struct pdn_ctx {
     int32_t *h_status = nullptr;  // pinned mirror
     DevBuf<char> l2_flush;
     SolveWork *solve = nullptr;
+    AssembleWork *asmw = nullptr;
+    PdnComm *comm = nullptr;      // set by pdn_comm_init (one rank per GPU); null = single GPU
+    DevBuf<int32_t> scan_tmp32;   // tile totals of the device-wide scans
+    DevBuf<int64_t> scan_tmp64;
 };
 
 #define PDN_LAUNCH(ctx, kernel, grid, block, smem, ...)                                         \
@@ -171,9 +177,14 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, doubl
 void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device);
 void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms);
 void pdn_solve_release(pdn_ctx *ctx);
+void pdn_assemble_release(pdn_ctx *ctx);
 
-// SpMV launcher shared by solve / diagnostics (pdn_spmv.cu): y = A x, optional fused dot.
-// rows [0, n_rows); if dot_with != nullptr, block partial sums of dot_with[i]*y[i] go to partials
-// (one per block) -- see pdn_spmv.cu.
-void pdn_launch_spmv(pdn_ctx *ctx, int64_t n_rows, const int32_t *indptr, const int32_t *indices,
-                     const double *data, const double *x, double *y);
+// multi-GPU plumbing (pdn_multi.cu); all collectives are enqueued on the context stream
+int pdn_comm_rank(const pdn_ctx *ctx);
+int pdn_comm_world(const pdn_ctx *ctx);
+void pdn_comm_release(pdn_ctx *ctx);
+void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count);
+void pdn_comm_allgatherv(pdn_ctx *ctx, double *vec, const int64_t *begin);
+void pdn_comm_exchange(pdn_ctx *ctx, const double *sendbuf, const int32_t *send_off, const int32_t *send_cnt,
+                       double *recvbuf, const int32_t *recv_off, const int32_t *recv_cnt);
+

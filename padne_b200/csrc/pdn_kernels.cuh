@@ -30,6 +30,7 @@ struct Scal {
     int32_t iter, done, breakdown, first;
     int32_t max_iter, pad0, pad1, pad2;
     unsigned int ticket[4];
+    double part[4];    // this rank's partial sums awaiting the all-reduce (multi-GPU)
 };
 
 enum Mode { PLAIN = 0, CG = 1, BICG_V = 2, BICG_T = 3, RESID = 4 };
@@ -109,19 +110,55 @@ __device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partial
 //   RESID : y = b - A x;       rr = y.y                                   aux0 = b
 // ------------------------------------------------------------------------------------------------
 #include "pdn_spmv.cuh"
+#include "pdn_sell.cuh"
+
+// scalar recurrences of the BiCGSTAB vector kernels (one thread, after the grid-wide reduction)
+__device__ __forceinline__ void bicg_x_finalize(const double (&acc)[3], Scal *sc) {
+    const double rho_new = acc[0], rr = acc[2];
+    sc->rr = rr;
+    sc->iter += 1;
+    if (rr <= sc->tol2) { sc->done = 1; return; }
+    if (sc->iter >= sc->max_iter) { sc->done = 2; return; }
+    const double beta = (rho_new / sc->rho) * (sc->alpha / sc->omega);
+    if (!(beta == beta) || !(fabs(beta) < 1e300) || sc->omega == 0.0) { sc->breakdown = 1; sc->done = 3; return; }
+    sc->rho_old = sc->rho;
+    sc->rho = rho_new;
+    sc->beta = beta;
+}
+__device__ __forceinline__ void bicg_init_finalize(const double (&acc)[3], Scal *sc) {
+    sc->rho = acc[0];
+    sc->rho_old = acc[0];
+    sc->rr = acc[0];
+    sc->omega = 1.0;
+    sc->alpha = 1.0;
+    if (acc[0] <= sc->tol2) sc->done = 1;
+}
+
+// Multi-GPU: the recurrence that follows an all-reduce of sc->part[0..2] (one thread).
+//   WHICH: 0..4 = spmv_finalize<Mode>, 5 = bicg_x_finalize, 6 = bicg_init_finalize, 7 = *out = part[0]
+template <int WHICH>
+__global__ void scalar_kernel(Scal *sc, double *out) {
+    if (WHICH != RESID && WHICH != 7 && WHICH != 6 && sc->done) return;
+    const double acc[3] = {sc->part[0], sc->part[1], sc->part[2]};
+    if (WHICH == 5) bicg_x_finalize(acc, sc);
+    else if (WHICH == 6) bicg_init_finalize(acc, sc);
+    else if (WHICH == 7) *out = acc[0];
+    else spmv_finalize<WHICH>(acc, sc);
+}
 
 // ------------------------------------------------------------------------------------------------
-// fused vector kernels (grid-stride, one element per thread per step)
+// fused vector kernels (grid-stride, one element per thread per step) over the rows [r0, n) this
+// rank owns (r0 = 0 and n = all rows on a single GPU)
 // ------------------------------------------------------------------------------------------------
 // Chronopoulos-Gear update:  p = z + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  z = dinv r
-__global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t n, const Scal *__restrict__ sc,
+__global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                         const double *__restrict__ dinv,
                                                         const double *__restrict__ w, double *__restrict__ z,
                                                         double *__restrict__ p, double *__restrict__ s,
                                                         double *__restrict__ x, double *__restrict__ r) {
     if (sc->done) return;
     const double alpha = sc->alpha, beta = sc->beta;
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         const double pi = z[i] + beta * p[i];
         const double si = w[i] + beta * s[i];
         const double ri = r[i] - alpha * si;
@@ -134,10 +171,10 @@ __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t n, const Scal *_
 }
 
 // r = b (x = 0 start) or given r;  z = dinv r;  p = s = 0
-__global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t n, const double *__restrict__ dinv,
+__global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, const double *__restrict__ dinv,
                                                       const double *__restrict__ r, double *__restrict__ z,
                                                       double *__restrict__ p, double *__restrict__ s) {
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         z[i] = dinv[i] * r[i];
         p[i] = 0.0;
         s[i] = 0.0;
@@ -145,13 +182,13 @@ __global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t n, const double *_
 }
 
 // BiCGSTAB step 2:  s = r - alpha v;  sh = dinv s
-__global__ void __launch_bounds__(RPB) bicg_s_kernel(int64_t n, const Scal *__restrict__ sc,
+__global__ void __launch_bounds__(RPB) bicg_s_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                      const double *__restrict__ dinv,
                                                      const double *__restrict__ r, const double *__restrict__ v,
                                                      double *__restrict__ s, double *__restrict__ sh) {
     if (sc->done) return;
     const double alpha = sc->alpha;
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         const double si = r[i] - alpha * v[i];
         s[i] = si;
         sh[i] = dinv[i] * si;
@@ -159,7 +196,8 @@ __global__ void __launch_bounds__(RPB) bicg_s_kernel(int64_t n, const Scal *__re
 }
 
 // BiCGSTAB step 4:  x += alpha ph + omega sh;  r = s - omega t;  rho_new = rhat.r;  rr = r.r
-__global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t n, Scal *sc, const double *__restrict__ ph,
+template <bool DIST>
+__global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t r0, int64_t n, Scal *sc, const double *__restrict__ ph,
                                                      const double *__restrict__ sh, const double *__restrict__ s,
                                                      const double *__restrict__ t, const double *__restrict__ rhat,
                                                      double *__restrict__ x, double *__restrict__ r,
@@ -168,7 +206,7 @@ __global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t n, Scal *sc, const 
     if (sc->done) return;
     const double alpha = sc->alpha, omega = sc->omega;
     double acc[3] = {0.0, 0.0, 0.0};
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         x[i] += alpha * ph[i] + omega * sh[i];
         const double ri = s[i] - omega * t[i];
         r[i] = ri;
@@ -177,26 +215,18 @@ __global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t n, Scal *sc, const 
     }
     if (!grid_reduce<3>(acc, partials, &sc->ticket[1], red)) return;
     if (threadIdx.x != 0) return;
-    const double rho_new = acc[0], rr = acc[2];
-    sc->rr = rr;
-    sc->iter += 1;
-    if (rr <= sc->tol2) { sc->done = 1; return; }
-    if (sc->iter >= sc->max_iter) { sc->done = 2; return; }
-    const double beta = (rho_new / sc->rho) * (sc->alpha / sc->omega);
-    if (!(beta == beta) || !(fabs(beta) < 1e300) || sc->omega == 0.0) { sc->breakdown = 1; sc->done = 3; return; }
-    sc->rho_old = sc->rho;
-    sc->rho = rho_new;
-    sc->beta = beta;
+    if (DIST) { sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2]; }
+    else bicg_x_finalize(acc, sc);
 }
 
 // BiCGSTAB step 5:  p = r + beta (p - omega v);  ph = dinv p
-__global__ void __launch_bounds__(RPB) bicg_p_kernel(int64_t n, const Scal *__restrict__ sc,
+__global__ void __launch_bounds__(RPB) bicg_p_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                      const double *__restrict__ dinv,
                                                      const double *__restrict__ r, const double *__restrict__ v,
                                                      double *__restrict__ p, double *__restrict__ ph) {
     if (sc->done) return;
     const double beta = sc->beta, omega = sc->omega;
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         const double pi = r[i] + beta * (p[i] - omega * v[i]);
         p[i] = pi;
         ph[i] = dinv[i] * pi;
@@ -204,13 +234,14 @@ __global__ void __launch_bounds__(RPB) bicg_p_kernel(int64_t n, const Scal *__re
 }
 
 // BiCGSTAB start from residual r:  rhat = r; p = r; ph = dinv p; rho = r.r; rr = r.r
-__global__ void __launch_bounds__(RPB) bicg_init_kernel(int64_t n, Scal *sc, const double *__restrict__ dinv,
+template <bool DIST>
+__global__ void __launch_bounds__(RPB) bicg_init_kernel(int64_t r0, int64_t n, Scal *sc, const double *__restrict__ dinv,
                                                         const double *__restrict__ r, double *__restrict__ rhat,
                                                         double *__restrict__ p, double *__restrict__ ph,
                                                         double *partials) {
     __shared__ double red[3][RPB / 32];
     double acc[3] = {0.0, 0.0, 0.0};
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         const double ri = r[i];
         rhat[i] = ri;
         p[i] = ri;
@@ -219,27 +250,26 @@ __global__ void __launch_bounds__(RPB) bicg_init_kernel(int64_t n, Scal *sc, con
     }
     if (!grid_reduce<3>(acc, partials, &sc->ticket[1], red)) return;
     if (threadIdx.x != 0) return;
-    sc->rho = acc[0];
-    sc->rho_old = acc[0];
-    sc->rr = acc[0];
-    sc->omega = 1.0;
-    sc->alpha = 1.0;
-    if (acc[0] <= sc->tol2) sc->done = 1;
+    if (DIST) { sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2]; }
+    else bicg_init_finalize(acc, sc);
 }
 
 // sum of squares (for ||b||, ||L v - r||)
-__global__ void __launch_bounds__(RPB) sumsq_kernel(int64_t n, const double *__restrict__ a,
+template <bool DIST>
+__global__ void __launch_bounds__(RPB) sumsq_kernel(int64_t r0, int64_t n, const double *__restrict__ a,
                                                     const double *__restrict__ b, Scal *sc, double *out,
                                                     double *partials) {
     // out = sum (a_i - b_i)^2   (b may be null)
     __shared__ double red[3][RPB / 32];
     double acc[3] = {0.0, 0.0, 0.0};
-    for (int64_t i = (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
+    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
         const double d = b ? a[i] - b[i] : a[i];
         acc[0] += d * d;
     }
     if (!grid_reduce<3>(acc, partials, &sc->ticket[2], red)) return;
-    if (threadIdx.x == 0) *out = acc[0];
+    if (threadIdx.x != 0) return;
+    if (DIST) sc->part[0] = acc[0];
+    else *out = acc[0];
 }
 
 }  // namespace pdnk

@@ -1,0 +1,177 @@
+// pdn_multi.cu -- multi-GPU plumbing: one process per GPU, NCCL over NVLink / NVSwitch.
+//
+// The north star partitions one large board across the GPUs of a box: contiguous row ranges of the
+// (permuted) reduced system, a halo exchange of the interface x-values before every SpMV and an
+// all-reduce of the fused Krylov dot products.  This file owns the communicator and the three
+// collective shapes the solver needs; the Krylov drivers in pdn_solve.cu enqueue them on the context
+// stream (they are captured into the same CUDA graph as the kernels).
+//
+// NCCL is resolved at run time with dlopen("libnccl.so.2"): inside a torch process that is the copy
+// torch already loaded (2.28.x), otherwise the system library.  The few NCCL types used here are
+// re-declared so the build needs no NCCL headers and the library no link-time NCCL dependency.
+#include <dlfcn.h>
+
+#include "pdn_common.cuh"
+
+namespace {
+
+// --- the slice of the NCCL ABI used here (nccl.h 2.27: enums and opaque types are stable) ----------
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+constexpr int kNcclSuccess = 0;
+constexpr int kNcclSum = 0;
+constexpr int kNcclInt32 = 2;     // ncclInt32
+constexpr int kNcclFloat64 = 8;   // ncclFloat64
+
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+
+NcclApi g_nccl;
+
+const NcclApi &nccl() {
+    if (g_nccl.handle) return g_nccl;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) PDN_FAIL(PDN_ECUDA, "comm: cannot load libnccl.so.2 (%s)", dlerror());
+#define PDN_SYM(name)                                                                    \
+    do {                                                                                 \
+        *(void **)(&g_nccl.name) = dlsym(h, "nccl" #name);                               \
+        if (!g_nccl.name) PDN_FAIL(PDN_ECUDA, "comm: libnccl lacks nccl" #name);          \
+    } while (0)
+    PDN_SYM(GetUniqueId);
+    PDN_SYM(CommInitRank);
+    PDN_SYM(CommDestroy);
+    PDN_SYM(AllReduce);
+    PDN_SYM(Broadcast);
+    PDN_SYM(Send);
+    PDN_SYM(Recv);
+    PDN_SYM(GroupStart);
+    PDN_SYM(GroupEnd);
+    PDN_SYM(GetErrorString);
+#undef PDN_SYM
+    g_nccl.handle = h;
+    return g_nccl;
+}
+
+#define PDN_NCCL(expr)                                                                            \
+    do {                                                                                          \
+        int _r = (expr);                                                                          \
+        if (_r != kNcclSuccess)                                                                   \
+            PDN_FAIL(PDN_ECUDA, "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, nccl().GetErrorString(_r)); \
+    } while (0)
+
+}  // namespace
+
+struct PdnComm {
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+};
+
+int pdn_comm_rank(const pdn_ctx *ctx) { return ctx->comm ? ctx->comm->rank : 0; }
+int pdn_comm_world(const pdn_ctx *ctx) { return ctx->comm ? ctx->comm->world : 1; }
+
+void pdn_comm_release(pdn_ctx *ctx) {
+    if (ctx->comm) {
+        if (ctx->comm->comm) nccl().CommDestroy(ctx->comm->comm);
+        delete ctx->comm;
+        ctx->comm = nullptr;
+    }
+}
+
+// in-place sum of `count` doubles on the context stream
+void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count) {
+    PDN_NCCL(nccl().AllReduce(buf, buf, (size_t)count, kNcclFloat64, kNcclSum, ctx->comm->comm, ctx->stream));
+}
+
+// vec[begin[k] .. begin[k+1]) is broadcast from rank k, for every k (an all-gather with ragged slices)
+void pdn_comm_allgatherv(pdn_ctx *ctx, double *vec, const int64_t *begin) {
+    const int world = ctx->comm->world;
+    PDN_NCCL(nccl().GroupStart());
+    for (int k = 0; k < world; k++) {
+        const int64_t cnt = begin[k + 1] - begin[k];
+        if (cnt > 0)
+            PDN_NCCL(nccl().Broadcast(vec + begin[k], vec + begin[k], (size_t)cnt, kNcclFloat64, k, ctx->comm->comm,
+                                      ctx->stream));
+    }
+    PDN_NCCL(nccl().GroupEnd());
+}
+
+// grouped point-to-point exchange: to/from peer k, send_cnt[k] doubles at sendbuf + send_off[k] and
+// recv_cnt[k] doubles at recvbuf + recv_off[k]
+void pdn_comm_exchange(pdn_ctx *ctx, const double *sendbuf, const int32_t *send_off, const int32_t *send_cnt,
+                       double *recvbuf, const int32_t *recv_off, const int32_t *recv_cnt) {
+    const int world = ctx->comm->world, me = ctx->comm->rank;
+    PDN_NCCL(nccl().GroupStart());
+    for (int k = 0; k < world; k++) {
+        if (k == me) continue;
+        if (send_cnt[k] > 0)
+            PDN_NCCL(nccl().Send(sendbuf + send_off[k], (size_t)send_cnt[k], kNcclFloat64, k, ctx->comm->comm, ctx->stream));
+        if (recv_cnt[k] > 0)
+            PDN_NCCL(nccl().Recv(recvbuf + recv_off[k], (size_t)recv_cnt[k], kNcclFloat64, k, ctx->comm->comm, ctx->stream));
+    }
+    PDN_NCCL(nccl().GroupEnd());
+}
+
+extern "C" {
+
+int pdn_comm_unique_id(void *out128) {
+    if (!out128) return PDN_EINVAL;
+    try {
+        ncclUniqueId id;
+        PDN_NCCL(nccl().GetUniqueId(&id));
+        memcpy(out128, &id, sizeof id);
+        return PDN_OK;
+    } catch (const pdn_error &e) {
+        fprintf(stderr, "pdn_comm_unique_id: %s\n", e.msg.c_str());
+        return e.code;
+    }
+}
+
+int pdn_comm_init(pdn_ctx *ctx, int rank, int world, const void *id128) {
+    return pdn_guard(ctx, [&] {
+        if (world < 1 || world > 32 || rank < 0 || rank >= world || !id128)
+            PDN_FAIL(PDN_EINVAL, "comm_init: rank %d of %d (1..32 ranks supported)", rank, world);
+        pdn_comm_release(ctx);
+        if (world == 1) return;
+        ncclUniqueId id;
+        memcpy(&id, id128, sizeof id);
+        PdnComm *c = new PdnComm();
+        c->rank = rank;
+        c->world = world;
+        ctx->comm = c;
+        PDN_NCCL(nccl().CommInitRank(&c->comm, world, id, rank));
+        // first use sets up the channels; do it outside any graph capture
+        DevBuf<double> tmp;
+        tmp.reserve(8);
+        PDN_CUDA(cudaMemsetAsync(tmp.p, 0, 8 * sizeof(double), ctx->stream));
+        pdn_comm_allreduce_sum(ctx, tmp.p, 4);
+        PDN_CUDA(cudaStreamSynchronize(ctx->stream));
+    });
+}
+
+int pdn_comm_destroy(pdn_ctx *ctx) {
+    return pdn_guard(ctx, [&] {
+        PDN_CUDA(cudaStreamSynchronize(ctx->stream));
+        pdn_comm_release(ctx);
+    });
+}
+
+int pdn_comm_info(pdn_ctx *ctx, int *rank, int *world) {
+    if (!ctx) return PDN_EINVAL;
+    if (rank) *rank = pdn_comm_rank(ctx);
+    if (world) *world = pdn_comm_world(ctx);
+    return PDN_OK;
+}
+
+}  // extern "C"

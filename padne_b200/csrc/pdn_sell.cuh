@@ -1,0 +1,269 @@
+// pdn_sell.cuh -- kernel (3a'): the Krylov loop's SpMV on a SELL-32-sigma copy of the reduced operator.
+//
+// Layout (built once per solve by the setup kernels at the bottom of this file):
+//   * rows are sorted by stored length (descending, stable) inside windows of SELL_WIN rows and the
+//     whole reduced system is permuted symmetrically with that order, so every Krylov vector lives
+//     in the permuted numbering and all per-row accesses stay unit-stride;
+//   * 32 consecutive rows form a slice, stored column-major and padded to the slice's longest row
+//     (after the sort the padding is ~0: mesh rows of equal length sit together);
+//   * lane l of a warp owns row 32*s + l: every load of the value / column arrays is one fully
+//     coalesced 256 B / 128 B request, x is gathered through L1/L2 (mesh-local numbering keeps the
+//     neighbours of a window inside a few KB), one DFMA per stored entry, no shared memory and no
+//     barrier in the inner loop, full occupancy hides the gather latency.
+// HBM traffic per row: 12 B per stored entry + 1/8 B of slice metadata + the vectors -- the
+// algorithmic figure of SURVEY.md 8d minus the 4 B row pointer.
+//
+// Work is split statically (contiguous slice ranges per CTA, CTA count = SMs x resident CTAs) so the
+// fused dot products are summed in a fixed order: results are bit-identical run to run.
+//
+// Included by pdn_kernels.cuh (namespace pdnk).
+#pragma once
+
+constexpr int SELL_C = 32;        // rows per slice = warp width
+constexpr int SELL_WIN = 1024;    // sorting window (rows); slices never straddle a window
+#ifndef PDN_SELL_BLK
+#define PDN_SELL_BLK 256
+#endif
+constexpr int SELL_BLK = PDN_SELL_BLK;     // threads per CTA of the SpMV
+constexpr int SELL_WARPS = SELL_BLK / 32;
+constexpr int SELL_MAXLEN = 1 << 20;
+#ifndef PDN_SELL_U
+#define PDN_SELL_U 5
+#endif
+#ifndef PDN_SELL_PF
+#define PDN_SELL_PF 0
+#endif
+#ifndef PDN_SELL_MINB
+#define PDN_SELL_MINB 4
+#endif
+constexpr int SELL_U = PDN_SELL_U;     // entries per row fetched per step
+constexpr int SELL_PF = PDN_SELL_PF;   // L2 prefetch distance in entries (12 B each) per CTA; 0 = off
+
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+struct SellOp {
+    int64_t n;                 // rows of the reduced system (permuted numbering)
+    int64_t row_begin, row_end;// rows this rank owns (multiples of SELL_WIN except the global end)
+    const int32_t *soff;       // [n_slices+1] entry offset of every slice (multiple of 32)
+    const uint32_t *smask;     // [n_slices] bit l: row 32*s+l is an override row (skipped here)
+    const int32_t *ci;         // column indices (permuted numbering), column-major inside a slice
+    const double *va;
+    int32_t n_special;         // override rows (constraint terminals), handled by CTA 0 of the owner
+    const int32_t *sp_row;     // [n_special] permuted row ids, ascending
+    const int32_t *sp_rp;      // [n_special+1]
+    const int32_t *sp_ci;      // permuted column ids
+    const double *sp_va;
+};
+
+// DIST = false: the last CTA to finish runs the scalar recurrence (single GPU).
+// DIST = true : the last CTA stores this rank's three partial sums to sc->part[] and the recurrence
+//               runs in scalar_kernel after the all-reduce (pdn_multi.cuh).
+template <int MODE, bool DIST>
+__global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(SellOp A, const double *__restrict__ x,
+                                                               double *__restrict__ y,
+                                                               const double *__restrict__ aux0, Scal *sc,
+                                                               double *partials) {
+    __shared__ double red[3][SELL_WARPS];
+    if (MODE != PLAIN && MODE != RESID) {
+        if (sc->done) return;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t s_begin = A.row_begin / SELL_C, s_end = (A.row_end + SELL_C - 1) / SELL_C;
+    const int64_t s_cnt = s_end - s_begin;
+    const int64_t s_lo = s_begin + (int64_t)blockIdx.x * s_cnt / gridDim.x;
+    const int64_t s_hi = s_begin + (int64_t)(blockIdx.x + 1) * s_cnt / gridDim.x;
+    double acc[3] = {0.0, 0.0, 0.0};
+
+    // The CTA's slices are one contiguous range [e_lo, e_hi) of the value / column arrays.  Every warp
+    // asks L2 for the lines SELL_PF entries ahead of the slice it is working on (same byte count as
+    // the slice, so the union of all requests is the CTA's range shifted by SELL_PF, each line once):
+    // the DRAM latency is paid by the prefetch, the loads below see L2 latency.
+    // (Measured on B200: any distance > 0 is SLOWER than none -- 10M DOF: 198 us without, 221 us at 1 Ki,
+    // 259 us at 4 Ki, 302 us at 16 Ki entries -- so it is compiled out by default, SELL_PF = 0.)
+    const int32_t e_lo = SELL_PF > 0 && s_lo < s_hi ? __ldg(&A.soff[s_lo]) : 0,
+                  e_hi = SELL_PF > 0 && s_lo < s_hi ? __ldg(&A.soff[s_hi]) : 0;
+    if (SELL_PF > 0) {
+        const int32_t e_pf = e_lo + SELL_PF < e_hi ? e_lo + SELL_PF : e_hi;
+        for (int32_t e = e_lo + threadIdx.x * 16; e < e_pf; e += SELL_BLK * 16) prefetch_l2(A.va + e);
+        for (int32_t e = e_lo + threadIdx.x * 32; e < e_pf; e += SELL_BLK * 32) prefetch_l2(A.ci + e);
+    }
+
+    int64_t s = s_lo + warp;
+    int32_t off = 0, off1 = 0;
+    uint32_t mask = 0;
+    if (s < s_hi) { off = __ldg(&A.soff[s]); off1 = __ldg(&A.soff[s + 1]); mask = __ldg(&A.smask[s]); }
+    while (s < s_hi) {
+        // metadata of this warp's next slice is fetched before the entries of the current one
+        const int64_t sn = s + SELL_WARPS;
+        int32_t n_off = 0, n_off1 = 0;
+        uint32_t n_mask = 0;
+        if (sn < s_hi) { n_off = __ldg(&A.soff[sn]); n_off1 = __ldg(&A.soff[sn + 1]); n_mask = __ldg(&A.smask[sn]); }
+        if (SELL_PF > 0) {
+            const int32_t p0 = off + SELL_PF, p1 = off1 + SELL_PF < e_hi ? off1 + SELL_PF : e_hi;
+            for (int32_t e = p0 + lane * 16; e < p1; e += 32 * 16) prefetch_l2(A.va + e);
+            for (int32_t e = p0 + lane * 32; e < p1; e += 32 * 32) prefetch_l2(A.ci + e);
+        }
+
+        const int64_t row = s * SELL_C + lane;
+        const bool live = row < A.row_end && !((mask >> lane) & 1u);
+        double xi = 0.0, ai = 0.0;
+        if (live) {
+            if (MODE == CG) xi = x[row];
+            if (MODE != PLAIN) ai = aux0[row];
+        }
+        const int w = (off1 - off) >> 5;
+        const int32_t *__restrict__ cp = A.ci + off + lane;
+        const double *__restrict__ vp = A.va + off + lane;
+        double sum = 0.0;
+        // SELL_U entries per step, all loads of a step issued before the first use; w is
+        // warp-uniform, so the guards of the last step do not diverge
+        for (int k = 0; k < w; k += SELL_U) {
+            int32_t c[SELL_U];
+            double v[SELL_U], xx[SELL_U];
+#pragma unroll
+            for (int j = 0; j < SELL_U; j++) c[j] = k + j < w ? __ldg(cp + (k + j) * SELL_C) : 0;
+#pragma unroll
+            for (int j = 0; j < SELL_U; j++) v[j] = k + j < w ? __ldg(vp + (k + j) * SELL_C) : 0.0;
+#pragma unroll
+            for (int j = 0; j < SELL_U; j++) xx[j] = k + j < w ? __ldg(x + c[j]) : 0.0;
+#pragma unroll
+            for (int j = 0; j < SELL_U; j++) sum = fma(v[j], xx[j], sum);
+        }
+        if (live) row_epilogue<MODE>(row, sum, xi, ai, y, acc);
+        s = sn; off = n_off; off1 = n_off1; mask = n_mask;
+    }
+    // override rows (constraint terminals): CTA 0, one thread per row
+    if (blockIdx.x == 0) {
+        for (int32_t t = threadIdx.x; t < A.n_special; t += SELL_BLK) {
+            const int32_t row = A.sp_row[t];
+            if (row < A.row_begin || row >= A.row_end) continue;
+            double s2 = 0.0;
+            for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) s2 += A.sp_va[q] * x[A.sp_ci[q]];
+            row_epilogue<MODE>(row, s2, MODE == CG ? x[row] : 0.0, MODE != PLAIN ? aux0[row] : 0.0, y, acc);
+        }
+    }
+    if (MODE == PLAIN) return;
+    if (!grid_reduce<3, SELL_WARPS>(acc, partials, &sc->ticket[0], red)) return;
+    if (threadIdx.x != 0) return;
+    if (DIST) {
+        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
+    } else {
+        spmv_finalize<MODE>(acc, sc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// setup: reduced operator  A = -(Z^T L_nn Z)  (main part)  ->  SELL-32-sigma
+// ------------------------------------------------------------------------------------------------
+// stored length of every row of the reduced operator (-1: padding row beyond n, 0: override row)
+__global__ void __launch_bounds__(256) sell_len_kernel(int64_t n, int64_t n_pad, const int32_t *__restrict__ rp,
+                                                       const int32_t *__restrict__ ci,
+                                                       const int32_t *__restrict__ map,
+                                                       const uint8_t *__restrict__ special,
+                                                       int32_t *__restrict__ len) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n_pad; i += (int64_t)gridDim.x * 256) {
+        int32_t l = -1;
+        if (i < n) {
+            l = 0;
+            if (!special[i])
+                for (int32_t k = rp[i]; k < rp[i + 1]; k++) {
+                    const int32_t c = ci[k];
+                    l += (c < n && map[c] >= 0) ? 1 : 0;
+                }
+            if (l > SELL_MAXLEN) l = SELL_MAXLEN;
+        }
+        len[i] = l;
+    }
+}
+
+// one CTA per window: stable sort by descending length (bitonic network on unique keys)
+__global__ void __launch_bounds__(SELL_WIN) sell_sort_kernel(const int32_t *__restrict__ len,
+                                                            int32_t *__restrict__ perm,
+                                                            int32_t *__restrict__ inv) {
+    __shared__ uint32_t key[SELL_WIN];
+    const int t = threadIdx.x;
+    const int64_t base = (int64_t)blockIdx.x * SELL_WIN;
+    key[t] = ((uint32_t)(SELL_MAXLEN - len[base + t]) << 10) | (uint32_t)t;
+    for (int k = 2; k <= SELL_WIN; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            const int p = t ^ j;
+            if (p > t) {
+                const uint32_t a = key[t], b = key[p];
+                const bool up = (t & k) == 0;
+                if ((a > b) == up) { key[t] = b; key[p] = a; }
+            }
+        }
+    __syncthreads();
+    const int o = (int)(key[t] & (SELL_WIN - 1));
+    perm[base + t] = (int32_t)(base + o);
+    inv[base + o] = (int32_t)(base + t);
+}
+
+// entries per slice = 32 x the length of its first (longest) row
+__global__ void __launch_bounds__(256) sell_width_kernel(int64_t n_slices, const int32_t *__restrict__ len,
+                                                         const int32_t *__restrict__ perm,
+                                                         int32_t *__restrict__ cnt) {
+    for (int64_t s = (int64_t)blockIdx.x * 256 + threadIdx.x; s < n_slices; s += (int64_t)gridDim.x * 256) {
+        const int32_t l = len[perm[s * SELL_C]];
+        cnt[s] = l > 0 ? l * SELL_C : 0;
+    }
+}
+
+// one warp per slice: copy the rows in (negated, columns mapped through Z and the permutation),
+// pad, build the Jacobi diagonal and the override mask
+__global__ void __launch_bounds__(256) sell_fill_kernel(int64_t n, int64_t n_slices, const int32_t *__restrict__ rp,
+                                                        const int32_t *__restrict__ ci,
+                                                        const double *__restrict__ va,
+                                                        const int32_t *__restrict__ map,
+                                                        const uint8_t *__restrict__ special,
+                                                        const int32_t *__restrict__ perm,
+                                                        const int32_t *__restrict__ inv,
+                                                        const int32_t *__restrict__ soff,
+                                                        int32_t *__restrict__ o_ci, double *__restrict__ o_va,
+                                                        uint32_t *__restrict__ smask, double *__restrict__ dinv) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
+    const int64_t n_warp = ((int64_t)gridDim.x * 256) >> 5;
+    for (int64_t s = warp; s < n_slices; s += n_warp) {
+        const int64_t r = s * SELL_C + lane;
+        const int32_t off = soff[s], w = (soff[s + 1] - off) >> 5;
+        const int64_t old = perm[r];
+        const bool real = old < n;
+        const bool sp = real && special[old];
+        int32_t k = 0;
+        double d = 0.0;
+        if (real && !sp) {
+            for (int32_t q = rp[old]; q < rp[old + 1] && k < w; q++) {
+                const int32_t c = ci[q];
+                const int32_t mc = c < n ? map[c] : -1;
+                if (mc < 0) continue;
+                const int32_t nc = inv[mc];
+                const double v = -va[q];
+                o_ci[off + k * SELL_C + lane] = nc;
+                o_va[off + k * SELL_C + lane] = v;
+                if (nc == r) d += v;
+                k++;
+            }
+        }
+        for (; k < w; k++) {
+            o_ci[off + k * SELL_C + lane] = real ? (int32_t)r : 0;
+            o_va[off + k * SELL_C + lane] = 0.0;
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, sp);
+        if (lane == 0) smask[s] = m;
+        if (real) dinv[r] = sp ? 1.0 : 1.0 / d;   // override rows are set afterwards
+    }
+}
+
+__global__ void __launch_bounds__(256) remap_i32_kernel(int32_t k, const int32_t *__restrict__ inv, int32_t *idx) {
+    for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) idx[i] = inv[idx[i]];
+}
+__global__ void __launch_bounds__(256) flag_u8_kernel(int32_t k, const int32_t *__restrict__ idx, uint8_t *flag) {
+    for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) flag[idx[i]] = 1;
+}
+// b_new[r] = -g[perm[r]]
+__global__ void __launch_bounds__(256) permute_negate_kernel(int64_t n, const int32_t *__restrict__ perm,
+                                                             const double *__restrict__ g, double *__restrict__ b) {
+    for (int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x; r < n; r += (int64_t)gridDim.x * 256) b[r] = -g[perm[r]];
+}

@@ -17,8 +17,12 @@
 //        A u = b,   A = -(Z^T Q L_nn Z),   b = -Z^T Q (r_n - L_nn o).
 //
 // Z^T Q differs from the identity only on the "special" nodes T (constraint terminals and
-// regulator sense nodes), so A is stored as L_nn with remapped columns (device kernel) plus a tiny
-// override CSR for the rows in T (built on the host from the |T| fetched rows).  A is SPD when
+// regulator sense nodes), so A is stored as L_nn with remapped columns, converted on the device to
+// the SELL-32-sigma layout of pdn_sell.cuh (rows sorted by length inside 1024-row windows, the whole
+// reduced system permuted symmetrically), plus a tiny override CSR for the rows in T (built on the
+// host from the |T| fetched rows).  With several GPUs (pdn_comm_init) every rank builds the same
+// operator and owns a contiguous range of sort windows in the Krylov loop: halo exchange of the
+// interface entries of the SpMV input, all-reduce of the fused dot products (pdn_multi.cu).  A is SPD when
 // B = C^T (Jacobi-PCG, Chronopoulos-Gear single-reduction form) and non-symmetric otherwise
 // (Jacobi-BiCGSTAB).  After convergence v = Z u + o, x is recovered, and ||L v - r||_2 of the
 // FULL system is reported exactly as solver.py:775.
@@ -70,10 +74,6 @@ __global__ void __launch_bounds__(BLK) gather_f64_kernel(int32_t k, const int32_
                                                          const double *__restrict__ src, double *out) {
     for (int32_t i = blockIdx.x * BLK + threadIdx.x; i < k; i += gridDim.x * BLK) out[i] = src[idx[i]];
 }
-__global__ void __launch_bounds__(BLK) flag_rows_kernel(int32_t k, const int32_t *__restrict__ idx, int32_t *rp) {
-    for (int32_t i = blockIdx.x * BLK + threadIdx.x; i < k; i += gridDim.x * BLK) rp[idx[i]] = ~rp[idx[i]];
-}
-
 // row lengths (node columns only) of the rows in T, then their entries
 __global__ void __launch_bounds__(BLK) rowlen_kernel(int32_t k, int64_t n, const int32_t *__restrict__ rows,
                                                      const int32_t *__restrict__ rp, const int32_t *__restrict__ ci,
@@ -97,31 +97,6 @@ __global__ void __launch_bounds__(BLK) rowget_kernel(int32_t k, int64_t n, const
     }
 }
 
-// A_main = -L_nn with columns mapped through Z; fixed / extra columns are neutralised in place
-// (value 0, column = own row) so the pattern and the row pointers are shared with L.
-__global__ void __launch_bounds__(BLK) reduce_kernel(int64_t n, const int32_t *__restrict__ rp,
-                                                     const int32_t *__restrict__ ci, const double *__restrict__ va,
-                                                     const int32_t *__restrict__ map, int32_t *__restrict__ rp2,
-                                                     int32_t *__restrict__ ci2, double *__restrict__ va2,
-                                                     double *__restrict__ dinv) {
-    for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i <= n; i += (int64_t)gridDim.x * BLK) {
-        rp2[i] = rp[i];
-        if (i == n) break;
-        double d = 0.0;
-        for (int32_t k = rp[i]; k < rp[i + 1]; k++) {
-            const int32_t c = ci[k];
-            const int32_t mc = c < n ? map[c] : -1;
-            if (mc < 0) { ci2[k] = (int32_t)i; va2[k] = 0.0; }
-            else {
-                const double v = -va[k];
-                ci2[k] = mc; va2[k] = v;
-                if (mc == i) d += v;
-            }
-        }
-        dinv[i] = 1.0 / d;   // special rows are overwritten afterwards
-    }
-}
-
 __global__ void __launch_bounds__(BLK) check_dinv_kernel(int64_t n, const double *__restrict__ dinv, int32_t *status) {
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
         const double d = dinv[i];
@@ -131,22 +106,19 @@ __global__ void __launch_bounds__(BLK) check_dinv_kernel(int64_t n, const double
     }
 }
 
-__global__ void __launch_bounds__(BLK) negate_kernel(int64_t n, const double *__restrict__ g, double *__restrict__ b) {
-    for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) b[i] = -g[i];
-}
-
 __global__ void __launch_bounds__(BLK) ones_kernel(int64_t n, double *__restrict__ d) {
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) d[i] = 1.0;
 }
 
-// v_j = u[map_j] + o_j for nodes; extras start at 0
+// v_j = u[inv[map_j]] + o_j for nodes (u lives in the permuted numbering); extras start at 0
 __global__ void __launch_bounds__(BLK) expand_kernel(int64_t n, int64_t N, const int32_t *__restrict__ map,
+                                                     const int32_t *__restrict__ inv,
                                                      const double *__restrict__ o, const double *__restrict__ u,
                                                      double *__restrict__ v) {
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < N; i += (int64_t)gridDim.x * BLK) {
         if (i < n) {
             const int32_t m = map[i];
-            v[i] = (m >= 0 ? u[m] : 0.0) + o[i];
+            v[i] = (m >= 0 ? u[inv[m]] : 0.0) + o[i];
         } else {
             v[i] = 0.0;
         }
@@ -158,11 +130,26 @@ __global__ void __launch_bounds__(BLK) expand_kernel(int64_t n, int64_t N, const
 // ------------------------------------------------------------------------------------------------
 // per-context solve workspace
 // ------------------------------------------------------------------------------------------------
+// halo exchange plan of one rank (multi-GPU): which entries of a distributed vector it sends to /
+// receives from every peer, in ascending index order on both sides
+struct HaloPlan {
+    int world = 1, me = 0;
+    std::vector<int64_t> begin;                 // [world+1] first owned row of every rank
+    std::vector<int32_t> send_off, send_cnt, recv_off, recv_cnt;   // [world]
+    int32_t n_send = 0, n_recv = 0;
+    DevBuf<int32_t> send_idx, recv_idx;
+    DevBuf<double> sendbuf, recvbuf;
+};
+
 struct SolveWork {
-    // reduced operator
-    int64_t n = 0, N = 0;
-    DevBuf<int32_t> rp2, ci2, map, sp_row, sp_rp, sp_ci, tmp_i32a, tmp_i32b, tmp_i32c;
-    DevBuf<double> va2, dinv, sp_va, off, tmp_f64a, tmp_f64b;
+    // reduced operator (SELL-32-sigma, permuted numbering)
+    int64_t n = 0, N = 0, n_pad = 0, n_slices = 0;
+    DevBuf<int32_t> map, len, perm, inv, scnt, soff, s_ci, sp_row, sp_row_old, sp_rp, sp_ci, tmp_i32a, tmp_i32b, tmp_i32c;
+    DevBuf<int32_t> t_ptr_d, t_ci_d, halo_col, halo_mask;
+    DevBuf<double> t_va_d;
+    DevBuf<uint32_t> smask, needmask;
+    DevBuf<uint8_t> special;
+    DevBuf<double> s_va, dinv, sp_va, off, tmp_f64a, tmp_f64b;
     int32_t n_special = 0;
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
@@ -171,7 +158,10 @@ struct SolveWork {
     Scal *h_sc = nullptr;  // pinned
     double *d_out = nullptr;
     bool have_operator = false;
-    Operator A{};
+    SellOp A{};
+    int sell_grid = 0;     // CTAs of the SELL SpMV (SMs x resident CTAs)
+    HaloPlan halo;
+    int64_t row_begin = 0, row_end = 0;   // rows of the Krylov loop this rank owns
     ~SolveWork() {
         if (d_sc) cudaFree(d_sc);
         if (h_sc) cudaFreeHost(h_sc);
@@ -197,6 +187,7 @@ static SolveWork *get_work(pdn_ctx *ctx) {
     return ctx->solve;
 }
 
+// ---- CSR-stream kernel (pdn_spmv.cuh): the FULL system (setup, recovery, diagnostics) -----------------
 static int spmv_grid(const pdn_ctx *ctx, int64_t n) {
     int64_t nb = (n + SROWS - 1) / SROWS;
     int per_sm = (int)((227 * 1024) / (SPMV_SMEM + 1024));
@@ -226,6 +217,60 @@ static void launch_spmv(pdn_ctx *ctx, const Operator &A, const double *x, double
         configured = true;
     }
     PDN_LAUNCH(ctx, spmv_kernel<MODE>, spmv_grid(ctx, A.n), STHREADS, SPMV_SMEM, A, x, y, aux, w->d_sc, w->partials.p);
+}
+
+// ---- SELL kernel (pdn_sell.cuh): the reduced operator of the Krylov loop -----------------------------
+static int sell_grid_size(pdn_ctx *ctx) {
+    static int per_sm = 0;
+    if (!per_sm) {
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sell_spmv_kernel<CG, false>, SELL_BLK, 0));
+        if (per_sm < 1) per_sm = 1;
+    }
+    int64_t g = (int64_t)ctx->n_sm * per_sm;
+    return (int)(g < MAX_PART ? g : MAX_PART);
+}
+
+static bool is_dist(const pdn_ctx *ctx) { return pdn_comm_world(ctx) > 1; }
+
+// y = A x (+ fused dots) over the rows this rank owns.  Multi-GPU: the partial sums are all-reduced and
+// the scalar recurrence runs in scalar_kernel; x must already hold the halo entries.
+template <int MODE>
+static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
+    int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+    int grid = (int)std::min<int64_t>(w->sell_grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
+    if (is_dist(ctx)) {
+        auto kern = sell_spmv_kernel<MODE, true>;
+        PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+        if (MODE != PLAIN) {
+            pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
+            PDN_LAUNCH(ctx, scalar_kernel<MODE>, 1, 1, 0, w->d_sc, w->d_out);
+        }
+    } else {
+        auto kern = sell_spmv_kernel<MODE, false>;
+        PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+    }
+}
+
+// refresh the halo entries of a distributed vector (no-op on a single GPU)
+__global__ void __launch_bounds__(256) halo_pack_kernel(int32_t k, const int32_t *__restrict__ idx,
+                                                        const double *__restrict__ vec, double *__restrict__ buf) {
+    for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) buf[i] = vec[idx[i]];
+}
+__global__ void __launch_bounds__(256) halo_unpack_kernel(int32_t k, const int32_t *__restrict__ idx,
+                                                          const double *__restrict__ buf, double *__restrict__ vec) {
+    for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) vec[idx[i]] = buf[i];
+}
+
+static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
+    if (!is_dist(ctx)) return;
+    HaloPlan &h = w->halo;
+    if (h.n_send > 0)
+        PDN_LAUNCH(ctx, halo_pack_kernel, pdn_grid(ctx, h.n_send, 256, 4), 256, 0, h.n_send, h.send_idx.p, vec, h.sendbuf.p);
+    if (h.n_send > 0 || h.n_recv > 0)
+        pdn_comm_exchange(ctx, h.sendbuf.p, h.send_off.data(), h.send_cnt.data(), h.recvbuf.p, h.recv_off.data(),
+                          h.recv_cnt.data());
+    if (h.n_recv > 0)
+        PDN_LAUNCH(ctx, halo_unpack_kernel, pdn_grid(ctx, h.n_recv, 256, 4), 256, 0, h.n_recv, h.recv_idx.p, h.recvbuf.p, vec);
 }
 
 static void fetch_scal(pdn_ctx *ctx, SolveWork *w) {
@@ -458,39 +503,56 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w) {
     PDN_CUDA(cudaMemcpyAsync(w->d_sc, w->h_sc, sizeof(Scal), cudaMemcpyHostToDevice, ctx->stream));
 }
 
+// one iteration = SpMV with fused dots (+ halo exchange and all-reduce on several GPUs) + vector update
 void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
-    const int64_t n = w->n;
-    launch_spmv<CG>(ctx, w->A, w->z.p, w->w.p, w->r.p, w);
-    PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, n, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
+    const int64_t r0 = w->row_begin, r1 = w->row_end;
+    halo_exchange(ctx, w, w->z.p);
+    launch_sell<CG>(ctx, w, w->z.p, w->w.p, w->r.p);
+    PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                w->x.p, w->r.p);
 }
 
 void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
-    const int64_t n = w->n;
-    launch_spmv<BICG_V>(ctx, w->A, w->ph.p, w->vv.p, w->rhat.p, w);
-    PDN_LAUNCH(ctx, bicg_s_kernel, vgrid, RPB, 0, n, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->s.p, w->sh.p);
-    launch_spmv<BICG_T>(ctx, w->A, w->sh.p, w->tt.p, w->s.p, w);
-    PDN_LAUNCH(ctx, bicg_x_kernel, vgrid, RPB, 0, n, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p, w->rhat.p,
-               w->x.p, w->r.p, w->partials.p);
-    PDN_LAUNCH(ctx, bicg_p_kernel, vgrid, RPB, 0, n, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->p.p, w->ph.p);
+    const int64_t r0 = w->row_begin, r1 = w->row_end;
+    const bool dist = is_dist(ctx);
+    halo_exchange(ctx, w, w->ph.p);
+    launch_sell<BICG_V>(ctx, w, w->ph.p, w->vv.p, w->rhat.p);
+    PDN_LAUNCH(ctx, bicg_s_kernel, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->s.p, w->sh.p);
+    halo_exchange(ctx, w, w->sh.p);
+    launch_sell<BICG_T>(ctx, w, w->sh.p, w->tt.p, w->s.p);
+    if (dist) {
+        PDN_LAUNCH(ctx, bicg_x_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p,
+                   w->rhat.p, w->x.p, w->r.p, w->partials.p);
+        pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
+        PDN_LAUNCH(ctx, scalar_kernel<5>, 1, 1, 0, w->d_sc, w->d_out);
+    } else {
+        PDN_LAUNCH(ctx, bicg_x_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p,
+                   w->rhat.p, w->x.p, w->r.p, w->partials.p);
+    }
+    PDN_LAUNCH(ctx, bicg_p_kernel, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->p.p, w->ph.p);
 }
 
 // Solve A x = b (x starts at 0).  method: PDN_METHOD_PCG or PDN_METHOD_BICGSTAB.
+// Multi-GPU: b, dinv and the operator are replicated; every rank iterates on its own rows and all
+// ranks see identical scalars (the all-reduce returns the same bits everywhere), so they take the
+// same decisions; x is all-gathered at the end.
 KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, double atol, int max_iter,
                         int check_every) {
     KrylovResult res;
     const int64_t n = w->n;
+    const int64_t r0 = w->row_begin, r1 = w->row_end;
+    const bool dist = is_dist(ctx);
     cudaStream_t st = ctx->stream;
-    const int vgrid = pdn_grid(ctx, n, RPB, 8);
+    const int vgrid = pdn_grid(ctx, r1 - r0, RPB, 8);
     cudaEvent_t ev0, ev1;
     PDN_CUDA(cudaEventCreate(&ev0));
     PDN_CUDA(cudaEventCreate(&ev1));
     PDN_CUDA(cudaEventRecord(ev0, st));
 
-    // ||b||
+    // ||b|| (b is replicated: no communication)
     reset_scal(ctx, w, 0.0, 0.0, max_iter);
-    PDN_LAUNCH(ctx, sumsq_kernel, vgrid, RPB, 0, n, w->b.p, (const double *)nullptr, w->d_sc, w->d_out,
-               w->partials.p);
+    PDN_LAUNCH(ctx, sumsq_kernel<false>, pdn_grid(ctx, n, RPB, 8), RPB, 0, (int64_t)0, n, w->b.p,
+               (const double *)nullptr, w->d_sc, w->d_out, w->partials.p);
     double bnorm2 = 0.0;
     PDN_CUDA(cudaMemcpyAsync(&bnorm2, w->d_out, sizeof(double), cudaMemcpyDeviceToHost, st));
     PDN_CUDA(cudaStreamSynchronize(st));
@@ -507,6 +569,17 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     if (atol * atol > tol2) tol2 = atol * atol;
     reset_scal(ctx, w, tol2, bnorm2, max_iter);
     PDN_CUDA(cudaMemcpyAsync(w->r.p, w->b.p, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    if (dist) {
+        // the halo entries of the SpMV inputs are written by the exchange only; start them defined.
+        // One exchange outside the capture also lets NCCL set up its point-to-point channels.
+        PDN_CUDA(cudaMemsetAsync(w->z.p, 0, n * sizeof(double), st));
+        if (method == PDN_METHOD_BICGSTAB) {
+            PDN_CUDA(cudaMemsetAsync(w->ph.p, 0, n * sizeof(double), st));
+            PDN_CUDA(cudaMemsetAsync(w->sh.p, 0, n * sizeof(double), st));
+        }
+        halo_exchange(ctx, w, w->z.p);
+        PDN_CUDA(cudaStreamSynchronize(st));
+    }
 
     // one CUDA graph = check_every iterations; kernels turn into no-ops once sc->done is set
     cudaGraph_t graph = nullptr;
@@ -529,7 +602,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         PDN_CUDA(cudaGraphInstantiate(&exec, graph, 0));
         ctx->launches = launches_before;  // capture is not execution
     };
-    const int per_iter = method == PDN_METHOD_PCG ? 2 : 5;
+    const int per_iter = (method == PDN_METHOD_PCG ? 2 : 5) + (dist ? (method == PDN_METHOD_PCG ? 3 : 7) : 0);
     build_graph();
 
     auto cleanup = [&]() {
@@ -544,11 +617,17 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         double best_rr = -1.0;
         for (int attempt = 0;; attempt++) {
             // start / restart from the current residual r
-            if (method == PDN_METHOD_PCG)
-                PDN_LAUNCH(ctx, cg_init_kernel, vgrid, RPB, 0, n, w->dinv.p, w->r.p, w->z.p, w->p.p, w->s.p);
-            else
-                PDN_LAUNCH(ctx, bicg_init_kernel, vgrid, RPB, 0, n, w->d_sc, w->dinv.p, w->r.p, w->rhat.p, w->p.p,
-                           w->ph.p, w->partials.p);
+            if (method == PDN_METHOD_PCG) {
+                PDN_LAUNCH(ctx, cg_init_kernel, vgrid, RPB, 0, r0, r1, w->dinv.p, w->r.p, w->z.p, w->p.p, w->s.p);
+            } else if (dist) {
+                PDN_LAUNCH(ctx, bicg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->rhat.p,
+                           w->p.p, w->ph.p, w->partials.p);
+                pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
+                PDN_LAUNCH(ctx, scalar_kernel<6>, 1, 1, 0, w->d_sc, w->d_out);
+            } else {
+                PDN_LAUNCH(ctx, bicg_init_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->rhat.p,
+                           w->p.p, w->ph.p, w->partials.p);
+            }
             while (true) {
                 PDN_CUDA(cudaGraphLaunch(exec, st));
                 fetch_scal(ctx, w);
@@ -557,7 +636,8 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 if (w->h_sc->done) break;
             }
             // true residual of the current x
-            launch_spmv<RESID>(ctx, w->A, w->x.p, w->r.p, w->b.p, w);
+            halo_exchange(ctx, w, w->x.p);
+            launch_sell<RESID>(ctx, w, w->x.p, w->r.p, w->b.p);
             fetch_scal(ctx, w);
             const double rr_true = w->h_sc->rr;
             res.rel_residual = sqrt(rr_true / bnorm2);
@@ -581,6 +661,14 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     } catch (...) {
         cleanup();
         throw;
+    }
+    if (dist) {   // every rank needs the whole u for the (replicated) recovery step
+        try {
+            pdn_comm_allgatherv(ctx, w->x.p, w->halo.begin.data());
+        } catch (...) {
+            cleanup();
+            throw;
+        }
     }
     PDN_CUDA(cudaEventRecord(ev1, st));
     PDN_CUDA(cudaEventSynchronize(ev1));
@@ -614,6 +702,116 @@ void upload(pdn_ctx *ctx, DevBuf<T> &buf, const std::vector<T> &h) {
 }
 
 }  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// multi-GPU: halo plan.  Every rank holds the same operator, so every rank can derive both what it
+// needs from each peer and what each peer needs from it, with no negotiation: needmask[c] gets bit k
+// when a row owned by rank k references column c owned by somebody else.
+// ------------------------------------------------------------------------------------------------
+struct RowPart {
+    int world;
+    int64_t begin[33];
+    __host__ __device__ int owner(int64_t r) const {
+        int k = 0;
+        while (k + 1 < world && r >= begin[k + 1]) k++;
+        return k;
+    }
+};
+
+__global__ void __launch_bounds__(256) halo_mark_kernel(SellOp A, int64_t n_slices, RowPart part,
+                                                        uint32_t *__restrict__ needmask) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
+    const int64_t n_warp = ((int64_t)gridDim.x * 256) >> 5;
+    for (int64_t s = warp; s < n_slices; s += n_warp) {
+        const int64_t r = s * SELL_C + lane;
+        if (r >= A.n) continue;
+        const int32_t off = A.soff[s], w = (A.soff[s + 1] - off) >> 5;
+        const int ko = part.owner(r);
+        const int64_t lo = part.begin[ko], hi = part.begin[ko + 1];
+        for (int32_t k = 0; k < w; k++) {
+            const int32_t c = A.ci[off + k * SELL_C + lane];
+            if (c < lo || c >= hi) atomicOr(&needmask[c], 1u << ko);
+        }
+    }
+    // override rows
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < A.n_special; t += (int64_t)gridDim.x * 256) {
+        const int ko = part.owner(A.sp_row[t]);
+        const int64_t lo = part.begin[ko], hi = part.begin[ko + 1];
+        for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) {
+            const int32_t c = A.sp_ci[q];
+            if (c < lo || c >= hi) atomicOr(&needmask[c], 1u << ko);
+        }
+    }
+}
+
+// append (column, mask) of every marked column; with cap == 0 it only counts
+__global__ void __launch_bounds__(256) halo_collect_kernel(int64_t n, const uint32_t *__restrict__ needmask, int32_t cap,
+                                                           int32_t *count, int32_t *__restrict__ o_col,
+                                                           int32_t *__restrict__ o_mask) {
+    for (int64_t c = (int64_t)blockIdx.x * 256 + threadIdx.x; c < n; c += (int64_t)gridDim.x * 256) {
+        const uint32_t m = needmask[c];
+        if (!m) continue;
+        const int32_t slot = atomicAdd(count, 1);
+        if (slot < cap) { o_col[slot] = (int32_t)c; o_mask[slot] = (int32_t)m; }
+    }
+}
+
+static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/) {
+    cudaStream_t st = ctx->stream;
+    HaloPlan &h = w->halo;
+    const int world = h.world, me = h.me;
+    const int64_t n = w->n;
+    RowPart part{};
+    part.world = world;
+    for (int k = 0; k <= world; k++) part.begin[k] = h.begin[k];
+    w->needmask.reserve((size_t)n);
+    PDN_CUDA(cudaMemsetAsync(w->needmask.p, 0, (size_t)n * sizeof(uint32_t), st));
+    PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
+               w->needmask.p);
+    w->tmp_i32a.reserve(4);
+    int32_t cnt = 0;
+    PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, sizeof(int32_t), st));
+    PDN_LAUNCH(ctx, halo_collect_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->needmask.p, 0, w->tmp_i32a.p,
+               (int32_t *)nullptr, (int32_t *)nullptr);
+    PDN_CUDA(cudaMemcpyAsync(&cnt, w->tmp_i32a.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    std::vector<std::pair<int32_t, uint32_t>> marked((size_t)cnt);
+    if (cnt > 0) {
+        w->halo_col.reserve((size_t)cnt);
+        w->halo_mask.reserve((size_t)cnt);
+        PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, sizeof(int32_t), st));
+        PDN_LAUNCH(ctx, halo_collect_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->needmask.p, cnt, w->tmp_i32a.p,
+                   w->halo_col.p, w->halo_mask.p);
+        std::vector<int32_t> col(cnt), mask(cnt);
+        PDN_CUDA(cudaMemcpyAsync(col.data(), w->halo_col.p, cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaMemcpyAsync(mask.data(), w->halo_mask.p, cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        for (int32_t i = 0; i < cnt; i++) marked[i] = {col[i], (uint32_t)mask[i]};
+        std::sort(marked.begin(), marked.end());
+    }
+    h.send_off.assign(world, 0); h.send_cnt.assign(world, 0);
+    h.recv_off.assign(world, 0); h.recv_cnt.assign(world, 0);
+    std::vector<int32_t> send_idx, recv_idx;
+    for (int k = 0; k < world; k++) {
+        h.send_off[k] = (int32_t)send_idx.size();
+        h.recv_off[k] = (int32_t)recv_idx.size();
+        if (k == me) continue;
+        for (const auto &cm : marked) {
+            const int owner = part.owner(cm.first);
+            if (owner == me && (cm.second >> k) & 1u) send_idx.push_back(cm.first);   // peer k reads my entry
+            if (owner == k && (cm.second >> me) & 1u) recv_idx.push_back(cm.first);   // I read peer k's entry
+        }
+        h.send_cnt[k] = (int32_t)send_idx.size() - h.send_off[k];
+        h.recv_cnt[k] = (int32_t)recv_idx.size() - h.recv_off[k];
+    }
+    h.n_send = (int32_t)send_idx.size();
+    h.n_recv = (int32_t)recv_idx.size();
+    upload(ctx, h.send_idx, send_idx);
+    upload(ctx, h.recv_idx, recv_idx);
+    h.sendbuf.reserve((size_t)h.n_send + 1);
+    h.recvbuf.reserve((size_t)h.n_recv + 1);
+}
 
 void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, double *v_out, pdn_info *info,
                     bool on_device) {
@@ -725,22 +923,43 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     PDN_LAUNCH(ctx, iota_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, w->map.p);
     PDN_CUDA(cudaMemsetAsync(w->off.p, 0, N * sizeof(double), st));
     std::vector<int32_t> h_T(E.T.begin(), E.T.end()), h_rep(E.rep.begin(), E.rep.end());
-    upload(ctx, w->sp_row, h_T);
+    upload(ctx, w->sp_row_old, h_T);    // original numbering (setup, recovery)
+    upload(ctx, w->sp_row, h_T);        // mapped to the permuted numbering once the permutation exists
     upload(ctx, w->tmp_i32b, h_rep);
     upload(ctx, w->tmp_f64a, E.off);
     if (nT > 0) {
-        PDN_LAUNCH(ctx, scatter_i32_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->tmp_i32b.p, w->map.p);
-        PDN_LAUNCH(ctx, scatter_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->tmp_f64a.p, w->off.p);
+        PDN_LAUNCH(ctx, scatter_i32_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row_old.p, w->tmp_i32b.p, w->map.p);
+        PDN_LAUNCH(ctx, scatter_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row_old.p, w->tmp_f64a.p, w->off.p);
     }
 
-    // main part of the reduced operator + Jacobi diagonal
-    const int64_t nnz_n = (int64_t)c_ptr[0];  // entries of the node rows
-    w->rp2.reserve((size_t)n + 1);
-    w->ci2.reserve((size_t)nnz_n + 1);
-    w->va2.reserve((size_t)nnz_n + 1);
-    w->dinv.reserve((size_t)n);
-    PDN_LAUNCH(ctx, reduce_kernel, pdn_grid(ctx, n + 1, BLK, 8), BLK, 0, n, L.indptr.p, L.indices.p, L.data.p, w->map.p,
-               w->rp2.p, w->ci2.p, w->va2.p, w->dinv.p);
+    // main part of the reduced operator -> SELL-32-sigma (pdn_sell.cuh) + Jacobi diagonal
+    const int64_t n_pad = (n + SELL_WIN - 1) / SELL_WIN * SELL_WIN, n_slices = n_pad / SELL_C;
+    w->n_pad = n_pad;
+    w->n_slices = n_slices;
+    w->special.reserve((size_t)n_pad);
+    w->len.reserve((size_t)n_pad);
+    w->perm.reserve((size_t)n_pad);
+    w->inv.reserve((size_t)n_pad);
+    w->scnt.reserve((size_t)n_slices);
+    w->soff.reserve((size_t)n_slices + 1);
+    w->smask.reserve((size_t)n_slices);
+    w->dinv.reserve((size_t)n_pad);
+    PDN_CUDA(cudaMemsetAsync(w->special.p, 0, (size_t)n_pad, st));
+    if (nT > 0) PDN_LAUNCH(ctx, flag_u8_kernel, pdn_blocks(nT, 256), 256, 0, nT, w->sp_row_old.p, w->special.p);
+    PDN_LAUNCH(ctx, sell_len_kernel, pdn_grid(ctx, n_pad, 256, 8), 256, 0, n, n_pad, L.indptr.p, L.indices.p, w->map.p,
+               w->special.p, w->len.p);
+    PDN_LAUNCH(ctx, sell_sort_kernel, (int)(n_pad / SELL_WIN), SELL_WIN, 0, w->len.p, w->perm.p, w->inv.p);
+    PDN_LAUNCH(ctx, sell_width_kernel, pdn_grid(ctx, n_slices, 256, 8), 256, 0, n_slices, w->len.p, w->perm.p, w->scnt.p);
+    pdn_exclusive_scan_i32(ctx, w->scnt.p, n_slices, w->soff.p);
+    int32_t sell_total = 0;
+    PDN_CUDA(cudaMemcpyAsync(&sell_total, w->soff.p + n_slices, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    if (sell_total < 0) PDN_FAIL(PDN_EUNSUPPORTED, "solve: padded operator exceeds int32 indexing");
+    w->s_ci.reserve((size_t)sell_total + 64);
+    w->s_va.reserve((size_t)sell_total + 64);
+    PDN_LAUNCH(ctx, sell_fill_kernel, pdn_grid(ctx, n_slices * 32, 256, 8), 256, 0, n, n_slices, L.indptr.p, L.indices.p,
+               L.data.p, w->map.p, w->special.p, w->perm.p, w->inv.p, w->soff.p, w->s_ci.p, w->s_va.p, w->smask.p,
+               w->dinv.p);
 
     // g = r_n - L_nn o
     w->full_a.reserve((size_t)N);
@@ -753,23 +972,23 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     std::vector<double> t_va, g_T(nT > 0 ? nT : 1, 0.0);
     if (nT > 0) {
         w->tmp_i32c.reserve(nT + 1);
-        PDN_LAUNCH(ctx, rowlen_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, n, w->sp_row.p, L.indptr.p, L.indices.p, w->tmp_i32c.p);
+        PDN_LAUNCH(ctx, rowlen_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, n, w->sp_row_old.p, L.indptr.p, L.indices.p, w->tmp_i32c.p);
         std::vector<int32_t> len(nT);
         PDN_CUDA(cudaMemcpyAsync(len.data(), w->tmp_i32c.p, nT * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         w->tmp_f64b.reserve(nT);
-        PDN_LAUNCH(ctx, gather_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->full_a.p, w->tmp_f64b.p);
+        PDN_LAUNCH(ctx, gather_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row_old.p, w->full_a.p, w->tmp_f64b.p);
         PDN_CUDA(cudaMemcpyAsync(g_T.data(), w->tmp_f64b.p, nT * sizeof(double), cudaMemcpyDeviceToHost, st));
         PDN_CUDA(cudaStreamSynchronize(st));
         for (int t = 0; t < nT; t++) t_ptr[t + 1] = t_ptr[t] + len[t];
         const int32_t tot = t_ptr[nT];
         t_ci.resize(tot);
         t_va.resize(tot);
-        DevBuf<int32_t> d_tptr, d_tci;
-        DevBuf<double> d_tva;
+        DevBuf<int32_t> &d_tptr = w->t_ptr_d, &d_tci = w->t_ci_d;
+        DevBuf<double> &d_tva = w->t_va_d;
         upload(ctx, d_tptr, t_ptr);
         d_tci.reserve(tot + 1);
         d_tva.reserve(tot + 1);
-        PDN_LAUNCH(ctx, rowget_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, n, w->sp_row.p, L.indptr.p, L.indices.p, L.data.p,
+        PDN_LAUNCH(ctx, rowget_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, n, w->sp_row_old.p, L.indptr.p, L.indices.p, L.data.p,
                    d_tptr.p, d_tci.p, d_tva.p);
         if (tot > 0) {
             PDN_CUDA(cudaMemcpyAsync(t_ci.data(), d_tci.p, tot * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
@@ -817,9 +1036,13 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     upload(ctx, w->tmp_f64a, b_T);
     upload(ctx, w->tmp_f64b, dinv_T);
     w->b.reserve((size_t)n);
-    PDN_LAUNCH(ctx, negate_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, w->full_a.p, w->b.p);
+    PDN_LAUNCH(ctx, permute_negate_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->perm.p, w->full_a.p, w->b.p);
     if (nT > 0) {
-        PDN_LAUNCH(ctx, flag_rows_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->rp2.p);
+        // override rows move to the permuted numbering
+        PDN_LAUNCH(ctx, remap_i32_kernel, pdn_blocks(nT, 256), 256, 0, nT, w->inv.p, w->sp_row.p);
+        if (!r_ci.empty())
+            PDN_LAUNCH(ctx, remap_i32_kernel, pdn_blocks((int64_t)r_ci.size(), 256), 256, 0, (int32_t)r_ci.size(),
+                       w->inv.p, w->sp_ci.p);
         PDN_LAUNCH(ctx, scatter_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->tmp_f64a.p, w->b.p);
         PDN_LAUNCH(ctx, scatter_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->tmp_f64b.p, w->dinv.p);
     }
@@ -830,19 +1053,38 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         int stt = pdn_status_fetch(ctx, &detail);
         if (stt != 0) {
             pdn_status_reset(ctx);
-            PDN_FAIL(stt, "solve: node %lld has no conductance to any other node (%s)", (long long)detail, pdn_strerror(stt));
+            int32_t node = -1;
+            if (detail >= 0 && detail < n)
+                PDN_CUDA(cudaMemcpy(&node, w->perm.p + detail, sizeof(int32_t), cudaMemcpyDeviceToHost));
+            PDN_FAIL(stt, "solve: node %d has no conductance to any other node (%s)", node, pdn_strerror(stt));
         }
     }
     w->n_special = nT;
     w->A.n = n;
-    w->A.rp = w->rp2.p;
-    w->A.ci = w->ci2.p;
-    w->A.va = w->va2.p;
+    w->A.soff = w->soff.p;
+    w->A.smask = w->smask.p;
+    w->A.ci = w->s_ci.p;
+    w->A.va = w->s_va.p;
     w->A.n_special = nT;
     w->A.sp_row = w->sp_row.p;
     w->A.sp_rp = w->sp_rp.p;
     w->A.sp_ci = w->sp_ci.p;
     w->A.sp_va = w->sp_va.p;
+    w->sell_grid = sell_grid_size(ctx);
+    // rows of the Krylov loop this rank owns: whole sort windows, split evenly
+    {
+        const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
+        const int64_t n_win = n_pad / SELL_WIN;
+        HaloPlan &h = w->halo;
+        h.world = world;
+        h.me = me;
+        h.begin.assign(world + 1, 0);
+        for (int k = 0; k <= world; k++) h.begin[k] = std::min<int64_t>(n, (int64_t)k * n_win / world * SELL_WIN);
+        h.begin[world] = n;
+        w->row_begin = w->A.row_begin = h.begin[me];
+        w->row_end = w->A.row_end = h.begin[me + 1];
+        if (world > 1) build_halo_plan(ctx, w, (int32_t)r_ci.size());
+    }
     w->have_operator = true;
 
     // vectors
@@ -859,7 +1101,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
 
     // ---- recovery: v = Z u + o, x = M^-1 C (r_n - L_nn v), full residual -------------------------------
     double *d_v = on_device ? v_out : w->full_b.p;
-    PDN_LAUNCH(ctx, expand_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, n, N, w->map.p, w->off.p, w->x.p, d_v);
+    PDN_LAUNCH(ctx, expand_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, n, N, w->map.p, w->inv.p, w->off.p, w->x.p, d_v);
     std::vector<double> xcur(m > 0 ? m : 1, 0.0);
     if (m > 0) {
         reset_scal(ctx, w, 0.0, 0.0, 0);
@@ -867,7 +1109,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         std::vector<double> h_T(nT > 0 ? nT : 1, 0.0);
         if (nT > 0) {
             w->tmp_f64b.reserve(nT);
-            PDN_LAUNCH(ctx, gather_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->full_a.p, w->tmp_f64b.p);
+            PDN_LAUNCH(ctx, gather_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row_old.p, w->full_a.p, w->tmp_f64b.p);
             PDN_CUDA(cudaMemcpyAsync(h_T.data(), w->tmp_f64b.p, nT * sizeof(double), cudaMemcpyDeviceToHost, st));
             PDN_CUDA(cudaStreamSynchronize(st));
         }
@@ -922,8 +1164,9 @@ void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device) {
     PDN_CUDA(cudaStreamSynchronize(ctx->stream));
 }
 
-// Times the kernel that dominates the solve: the CG-mode SpMV (fused r.z, z.w, r.r) on the reduced
-// operator of the last pdn_solve; falls back to the full system when no solve has run yet.
+// Times the kernel that dominates the solve: the CG-mode SELL SpMV (fused r.z, z.w, r.r) on the reduced
+// operator of the last pdn_solve.  (Before any solve there is no reduced operator: the CSR-stream
+// kernel on the full system is timed instead.)
 //   mode 0: back-to-back launches (warm L2)
 //   mode 1: a >L2 buffer is written before every launch (cold L2)
 //   mode 2: in situ -- every SpMV is followed by the PCG vector update, exactly like one solver
@@ -931,8 +1174,9 @@ void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device) {
 void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
     SolveWork *w = get_work(ctx);
     cudaStream_t st = ctx->stream;
-    Operator A = w->have_operator ? w->A : full_operator(ctx, ctx->L.n);
-    const int64_t n = A.n;
+    const bool sell = w->have_operator;   // multi-GPU: this rank's rows only, no collectives
+    Operator Afull = full_operator(ctx, ctx->L.n);
+    const int64_t n = sell ? w->n : Afull.n;
     DevBuf<double> x, y, aux, v3, v4, v5, v6;
     x.reserve((size_t)n); y.reserve((size_t)n); aux.reserve((size_t)n);
     const int vgrid = pdn_grid(ctx, n, BLK, 8);
@@ -949,16 +1193,28 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
     // launches can be queued back to back; every SpMV gets its own event pair and the host
     // synchronises once at the end, like the kernels inside the solver's CUDA graph.
     reset_scal(ctx, w, 0.0, 0.0, -1);
-    for (int k = 0; k < 3; k++) launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
+    const int64_t r0 = sell ? w->row_begin : 0, r1 = sell ? w->row_end : n;
+    auto launch = [&]() {
+        if (sell) {
+            const int64_t slices = (r1 - r0 + SELL_C - 1) / SELL_C;
+            const int grid = (int)std::min<int64_t>(w->sell_grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
+            auto kern = sell_spmv_kernel<CG, false>;
+            PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x.p, y.p, aux.p, w->d_sc, w->partials.p);
+        } else {
+            launch_spmv<CG>(ctx, Afull, x.p, y.p, aux.p, w);
+        }
+    };
+    for (int k = 0; k < 3; k++) launch();
     std::vector<cudaEvent_t> ev(2 * (size_t)reps);
     for (auto &e : ev) PDN_CUDA(cudaEventCreate(&e));
     for (int k = 0; k < reps; k++) {
         if (mode == 1) pdn_flush_l2(ctx);
         PDN_CUDA(cudaEventRecord(ev[2 * k], st));
-        launch_spmv<CG>(ctx, A, x.p, y.p, aux.p, w);
+        launch();
         PDN_CUDA(cudaEventRecord(ev[2 * k + 1], st));
         if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
-            PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, n, w->d_sc, v6.p, y.p, x.p, v3.p, v4.p, v5.p, aux.p);
+            PDN_LAUNCH(ctx, cg_update_kernel, pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p, v3.p,
+                       v4.p, v5.p, aux.p);
     }
     PDN_CUDA(cudaStreamSynchronize(st));
     double total = 0.0;

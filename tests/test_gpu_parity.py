@@ -174,8 +174,11 @@ def test_solve_golden(ctx, path):
     assert info.method == ("bicgstab" if fs.has_regulator else "pcg")
     assert info.rel_residual <= RESIDUAL_RTOL
     assert voltage_error(v, d["v"], fs.n_nodes) <= VOLTAGE_RTOL
-    # extra unknowns: source currents and the ground current (solver.py:777)
-    assert np.allclose(v[fs.n_nodes:], d["v"][fs.n_nodes:], rtol=1e-6, atol=1e-7)
+    # extra unknowns: source currents and the ground current (solver.py:777); they are recovered from
+    # node residuals, so their absolute accuracy scales with the largest current (1.4e4 A in the
+    # regulator fixture)
+    i_scale = max(1.0, np.max(np.abs(d["v"][fs.n_nodes:])))
+    assert np.allclose(v[fs.n_nodes:], d["v"][fs.n_nodes:], rtol=1e-6, atol=1e-9 * i_scale)
     L = scipy.sparse.csr_matrix((data, indices, indptr), shape=(fs.N, fs.N))
     assert abs(info.residual_norm - np.linalg.norm(L @ v - rhs)) <= 1e-6 * max(info.residual_norm, 1e-12) + 1e-12
     assert info.residual_norm <= 1e-8 * max(1.0, np.linalg.norm(rhs))
