@@ -40,6 +40,31 @@ constexpr int SELL_U = PDN_SELL_U;     // entries per row fetched per step
 constexpr int SELL_PF = PDN_SELL_PF;   // L2 prefetch distance in entries (12 B each) per CTA; 0 = off
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// matrix stream: read-only, do not allocate in L1 (L1 is for the gathered x)
+#ifndef PDN_SELL_NOALLOC
+#define PDN_SELL_NOALLOC 1
+#endif
+__device__ __forceinline__ double ld_stream(const double *p) {
+#if PDN_SELL_NOALLOC
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+__device__ __forceinline__ int32_t ld_stream(const int32_t *p) {
+#if PDN_SELL_NOALLOC
+    int32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+#ifndef PDN_SELL_FAKEX
+#define PDN_SELL_FAKEX 0    // timing experiment only: 1 replaces the gather x[col] by x[row] (wrong results)
+#endif
 
 struct SellOp {
     int64_t n;                 // rows of the reduced system (permuted numbering)
@@ -121,11 +146,11 @@ __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(Sell
             int32_t c[SELL_U];
             double v[SELL_U], xx[SELL_U];
 #pragma unroll
-            for (int j = 0; j < SELL_U; j++) c[j] = k + j < w ? __ldg(cp + (k + j) * SELL_C) : 0;
+            for (int j = 0; j < SELL_U; j++) c[j] = k + j < w ? ld_stream(cp + (k + j) * SELL_C) : 0;
 #pragma unroll
-            for (int j = 0; j < SELL_U; j++) v[j] = k + j < w ? __ldg(vp + (k + j) * SELL_C) : 0.0;
+            for (int j = 0; j < SELL_U; j++) v[j] = k + j < w ? ld_stream(vp + (k + j) * SELL_C) : 0.0;
 #pragma unroll
-            for (int j = 0; j < SELL_U; j++) xx[j] = k + j < w ? __ldg(x + c[j]) : 0.0;
+            for (int j = 0; j < SELL_U; j++) xx[j] = k + j < w ? __ldg(x + (PDN_SELL_FAKEX ? (int32_t)row : c[j])) : 0.0;
 #pragma unroll
             for (int j = 0; j < SELL_U; j++) sum = fma(v[j], xx[j], sum);
         }
@@ -144,6 +169,182 @@ __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(Sell
     }
     if (MODE == PLAIN) return;
     if (!grid_reduce<3, SELL_WARPS>(acc, partials, &sc->ticket[0], red)) return;
+    if (threadIdx.x != 0) return;
+    if (DIST) {
+        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
+    } else {
+        spmv_finalize<MODE>(acc, sc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// TMA-ring variant (the default in the Krylov loop).
+//
+// The direct kernel above is bound by memory-level parallelism: a warp has one batch of matrix loads
+// in flight, then waits, then gathers (ncu: 45 % of DRAM peak, the stalls sit on the first use of the
+// column indices and of the gathered x).  Here every warp owns a private ring of SELL_NSLOT slice
+// buffers in shared memory.  A slice is ONE contiguous run of the value array and one of the column
+// array, so lane 0 streams the slices the warp will need SELL_NSLOT iterations from now with two
+// cp.async.bulk copies each (the TMA engine, UBLKCP in SASS; completion on a per-slot mbarrier) --
+// no registers are tied up and SELL_NSLOT slices per warp are always in flight.  The warp then reads its
+// column indices / values from shared memory (lane-contiguous: conflict-free), issues ALL gathers of
+// its row at once and runs the DFMA chain.  Warps never synchronise with each other.
+// Slices wider than SELL_WCAP (a node with many lumped elements) fall back to direct global loads.
+// Measured on B200 (in-situ SpMV, 2layer_1M / 8layer_10M, us): direct kernel with L1-allocating matrix
+// loads 33.4 / 202, direct with L1::no_allocate 28.6 / 194, this kernel 12 warps x 2 slots 29.3 / 185,
+// 8 warps x 3 slots 32.8 / 199, 4 warps x 6 slots 43.6 / 311: a DEEPER ring is slower (so is an L2
+// prefetch), more resident warps are faster -- the loop is bound by the x gathers per warp, not by the
+// matrix stream.
+// ------------------------------------------------------------------------------------------------
+#ifndef PDN_SELL_NSLOT
+#define PDN_SELL_NSLOT 2
+#endif
+#ifndef PDN_SELL_WCAP
+#define PDN_SELL_WCAP 10
+#endif
+#ifndef PDN_SELL_TW
+#define PDN_SELL_TW 12
+#endif
+#ifndef PDN_SELL_TMINB
+#define PDN_SELL_TMINB 2
+#endif
+constexpr int ST_NSLOT = PDN_SELL_NSLOT;
+constexpr int ST_WCAP = PDN_SELL_WCAP;
+constexpr int ST_WARPS = PDN_SELL_TW;
+constexpr int ST_BLK = ST_WARPS * 32;
+constexpr int ST_SLOT_ENT = ST_WCAP * SELL_C;
+constexpr int ST_SLOT_BYTES = ST_SLOT_ENT * 12;
+constexpr size_t ST_SMEM = (size_t)ST_WARPS * ST_NSLOT * ST_SLOT_BYTES + (size_t)ST_WARPS * ST_NSLOT * 8 + 3 * ST_WARPS * 8;
+
+template <int MODE, bool DIST>
+__global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp A, const double *__restrict__ x,
+                                                                     double *__restrict__ y,
+                                                                     const double *__restrict__ aux0, Scal *sc,
+                                                                     double *partials) {
+    extern __shared__ __align__(128) unsigned char st_smem[];
+    if (MODE != PLAIN && MODE != RESID) {
+        if (sc->done) return;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char *ring = st_smem + (size_t)warp * ST_NSLOT * ST_SLOT_BYTES;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(st_smem + (size_t)ST_WARPS * ST_NSLOT * ST_SLOT_BYTES) + warp * ST_NSLOT;
+    double(*red)[ST_WARPS] = reinterpret_cast<double(*)[ST_WARPS]>(
+        st_smem + (size_t)ST_WARPS * ST_NSLOT * ST_SLOT_BYTES + (size_t)ST_WARPS * ST_NSLOT * 8);
+    if (lane == 0) {
+        for (int q = 0; q < ST_NSLOT; q++) tma::mbar_init(&bars[q], 1);
+        tma::fence_barrier_init();
+    }
+    __syncwarp();
+
+    const int64_t s_begin = A.row_begin / SELL_C, s_end = (A.row_end + SELL_C - 1) / SELL_C;
+    const int64_t s_cnt = s_end - s_begin;
+    const int64_t s_lo = s_begin + (int64_t)blockIdx.x * s_cnt / gridDim.x;
+    const int64_t s_hi = s_begin + (int64_t)(blockIdx.x + 1) * s_cnt / gridDim.x;
+    // this warp's slices: s_lo + warp + j * ST_WARPS, j in [0, nj)
+    const int64_t nj = s_hi - s_lo > warp ? (s_hi - s_lo - warp + ST_WARPS - 1) / ST_WARPS : 0;
+    double acc[3] = {0.0, 0.0, 0.0};
+
+    // slice metadata arrives 32 slices at a time, one slice per lane (separate copies for the issue
+    // and the consume position, which sit SELL_NSLOT slices apart)
+    int32_t io0 = 0, io1 = 0, co0 = 0, co1 = 0;
+    uint32_t cmask = 0;
+    auto load_batch = [&](int64_t jb, int32_t &o0, int32_t &o1, uint32_t *m) {
+        const int64_t j = jb + lane;
+        o0 = o1 = 0;
+        if (m) *m = 0;
+        if (j < nj) {
+            const int64_t sl = s_lo + warp + j * ST_WARPS;
+            o0 = __ldg(&A.soff[sl]);
+            o1 = __ldg(&A.soff[sl + 1]);
+            if (m) *m = __ldg(&A.smask[sl]);
+        }
+    };
+    auto issue = [&](int64_t j) {   // all lanes call; lane 0 starts the copies of slice j
+        const int32_t o0 = __shfl_sync(0xffffffffu, io0, (int)(j & 31)), o1 = __shfl_sync(0xffffffffu, io1, (int)(j & 31));
+        const int32_t cnt = o1 - o0;
+        if (lane == 0 && cnt > 0 && cnt <= ST_SLOT_ENT) {
+            const int q = (int)(j % ST_NSLOT);
+            unsigned char *slot = ring + (size_t)q * ST_SLOT_BYTES;
+            tma::mbar_expect_tx(&bars[q], (uint32_t)cnt * 12u);
+            tma::bulk_g2s(slot, A.va + o0, (uint32_t)cnt * 8u, &bars[q]);
+            tma::bulk_g2s(slot + (size_t)ST_SLOT_ENT * 8, A.ci + o0, (uint32_t)cnt * 4u, &bars[q]);
+        }
+    };
+
+    load_batch(0, io0, io1, nullptr);
+    load_batch(0, co0, co1, &cmask);
+    int64_t jn = 0;
+    for (; jn < ST_NSLOT && jn < nj; jn++) issue(jn);
+    uint32_t phases = 0;   // bit q: parity of the next completion of slot q
+    for (int64_t j = 0; j < nj; j++) {
+        if (j && (j & 31) == 0) load_batch(j, co0, co1, &cmask);
+        const int32_t off = __shfl_sync(0xffffffffu, co0, (int)(j & 31)), off1 = __shfl_sync(0xffffffffu, co1, (int)(j & 31));
+        const uint32_t mask = __shfl_sync(0xffffffffu, cmask, (int)(j & 31));
+        const int64_t sl = s_lo + warp + j * ST_WARPS;
+        const int64_t row = sl * SELL_C + lane;
+        const bool live = row < A.row_end && !((mask >> lane) & 1u);
+        double xi = 0.0, ai = 0.0;
+        if (live) {
+            if (MODE == CG) xi = x[row];
+            if (MODE != PLAIN) ai = aux0[row];
+        }
+        const int w = (off1 - off) >> 5;
+        double sum = 0.0;
+        if (w > 0 && w <= ST_WCAP) {
+            const int q = (int)(j % ST_NSLOT);
+            const unsigned char *slot = ring + (size_t)q * ST_SLOT_BYTES;
+            const double *vs = reinterpret_cast<const double *>(slot) + lane;
+            const int32_t *cs = reinterpret_cast<const int32_t *>(slot + (size_t)ST_SLOT_ENT * 8) + lane;
+            tma::mbar_wait(&bars[q], (phases >> q) & 1u);
+            phases ^= 1u << q;
+            int32_t c[ST_WCAP];
+            double v[ST_WCAP], xx[ST_WCAP];
+#pragma unroll
+            for (int k = 0; k < ST_WCAP; k++) c[k] = k < w ? cs[k * SELL_C] : 0;
+#pragma unroll
+            for (int k = 0; k < ST_WCAP; k++) xx[k] = k < w ? __ldg(x + (PDN_SELL_FAKEX ? (int32_t)row : c[k])) : 0.0;
+#pragma unroll
+            for (int k = 0; k < ST_WCAP; k++) v[k] = k < w ? vs[k * SELL_C] : 0.0;
+#pragma unroll
+            for (int k = 0; k < ST_WCAP; k++) sum = fma(v[k], xx[k], sum);
+        } else if (w > 0) {   // wide slice: straight from global memory
+            const int32_t *__restrict__ cp = A.ci + off + lane;
+            const double *__restrict__ vp = A.va + off + lane;
+            for (int k = 0; k < w; k += SELL_U) {
+                int32_t c[SELL_U];
+                double v[SELL_U], xx[SELL_U];
+#pragma unroll
+                for (int i = 0; i < SELL_U; i++) c[i] = k + i < w ? __ldg(cp + (k + i) * SELL_C) : 0;
+#pragma unroll
+                for (int i = 0; i < SELL_U; i++) v[i] = k + i < w ? __ldg(vp + (k + i) * SELL_C) : 0.0;
+#pragma unroll
+                for (int i = 0; i < SELL_U; i++) xx[i] = k + i < w ? __ldg(x + c[i]) : 0.0;
+#pragma unroll
+                for (int i = 0; i < SELL_U; i++) sum = fma(v[i], xx[i], sum);
+            }
+        }
+        if (live) row_epilogue<MODE>(row, sum, xi, ai, y, acc);
+        // every lane has consumed its words of slot j % NSLOT: refill it with slice j + NSLOT
+        __syncwarp();
+        if (jn < nj) {
+            if ((jn & 31) == 0) load_batch(jn, io0, io1, nullptr);
+            issue(jn);
+            jn++;
+        }
+    }
+    __syncthreads();
+    // override rows (constraint terminals): CTA 0, one thread per row
+    if (blockIdx.x == 0) {
+        for (int32_t t = threadIdx.x; t < A.n_special; t += ST_BLK) {
+            const int32_t row = A.sp_row[t];
+            if (row < A.row_begin || row >= A.row_end) continue;
+            double s2 = 0.0;
+            for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) s2 += A.sp_va[q] * x[A.sp_ci[q]];
+            row_epilogue<MODE>(row, s2, MODE == CG ? x[row] : 0.0, MODE != PLAIN ? aux0[row] : 0.0, y, acc);
+        }
+    }
+    if (MODE == PLAIN) return;
+    if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
     if (threadIdx.x != 0) return;
     if (DIST) {
         sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];

@@ -159,7 +159,6 @@ struct SolveWork {
     double *d_out = nullptr;
     bool have_operator = false;
     SellOp A{};
-    int sell_grid = 0;     // CTAs of the SELL SpMV (SMs x resident CTAs)
     HaloPlan halo;
     int64_t row_begin = 0, row_end = 0;   // rows of the Krylov loop this rank owns
     ~SolveWork() {
@@ -219,35 +218,52 @@ static void launch_spmv(pdn_ctx *ctx, const Operator &A, const double *x, double
     PDN_LAUNCH(ctx, spmv_kernel<MODE>, spmv_grid(ctx, A.n), STHREADS, SPMV_SMEM, A, x, y, aux, w->d_sc, w->partials.p);
 }
 
-// ---- SELL kernel (pdn_sell.cuh): the reduced operator of the Krylov loop -----------------------------
-static int sell_grid_size(pdn_ctx *ctx) {
-    static int per_sm = 0;
-    if (!per_sm) {
-        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sell_spmv_kernel<CG, false>, SELL_BLK, 0));
-        if (per_sm < 1) per_sm = 1;
-    }
-    int64_t g = (int64_t)ctx->n_sm * per_sm;
-    return (int)(g < MAX_PART ? g : MAX_PART);
-}
+// ---- SELL kernels (pdn_sell.cuh): the reduced operator of the Krylov loop ------------------------------
+#ifndef PDN_SELL_TMA
+#define PDN_SELL_TMA 1     // 1: per-warp TMA ring kernel, 0: direct global-load kernel
+#endif
 
 static bool is_dist(const pdn_ctx *ctx) { return pdn_comm_world(ctx) > 1; }
+
+template <int MODE, bool DIST>
+static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
+    const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+#if PDN_SELL_TMA
+    auto kern = sell_tma_kernel<MODE, DIST>;
+    static int per_sm = 0;
+    if (!per_sm) {
+        PDN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM));
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, ST_BLK, ST_SMEM));
+        if (per_sm < 1) per_sm = 1;
+    }
+    int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
+    grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + ST_WARPS - 1) / ST_WARPS));
+    PDN_LAUNCH(ctx, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p);
+#else
+    auto kern = sell_spmv_kernel<MODE, DIST>;
+    static int per_sm = 0;
+    if (!per_sm) {
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, SELL_BLK, 0));
+        if (per_sm < 1) per_sm = 1;
+    }
+    int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
+    grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
+    PDN_LAUNCH(ctx, kern, (int)grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+#endif
+}
 
 // y = A x (+ fused dots) over the rows this rank owns.  Multi-GPU: the partial sums are all-reduced and
 // the scalar recurrence runs in scalar_kernel; x must already hold the halo entries.
 template <int MODE>
 static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
-    int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
-    int grid = (int)std::min<int64_t>(w->sell_grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
     if (is_dist(ctx)) {
-        auto kern = sell_spmv_kernel<MODE, true>;
-        PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+        launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
         if (MODE != PLAIN) {
             pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
             PDN_LAUNCH(ctx, scalar_kernel<MODE>, 1, 1, 0, w->d_sc, w->d_out);
         }
     } else {
-        auto kern = sell_spmv_kernel<MODE, false>;
-        PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+        launch_sell_kernel<MODE, false>(ctx, w, x, y, aux);
     }
 }
 
@@ -1070,7 +1086,6 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     w->A.sp_rp = w->sp_rp.p;
     w->A.sp_ci = w->sp_ci.p;
     w->A.sp_va = w->sp_va.p;
-    w->sell_grid = sell_grid_size(ctx);
     // rows of the Krylov loop this rank owns: whole sort windows, split evenly
     {
         const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
@@ -1196,10 +1211,7 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
     const int64_t r0 = sell ? w->row_begin : 0, r1 = sell ? w->row_end : n;
     auto launch = [&]() {
         if (sell) {
-            const int64_t slices = (r1 - r0 + SELL_C - 1) / SELL_C;
-            const int grid = (int)std::min<int64_t>(w->sell_grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
-            auto kern = sell_spmv_kernel<CG, false>;
-            PDN_LAUNCH(ctx, kern, grid, SELL_BLK, 0, w->A, x.p, y.p, aux.p, w->d_sc, w->partials.p);
+            launch_sell_kernel<CG, false>(ctx, w, x.p, y.p, aux.p);
         } else {
             launch_spmv<CG>(ctx, Afull, x.p, y.p, aux.p, w);
         }
