@@ -177,6 +177,8 @@ def main():
     ap.add_argument("--cpu-sample-n", type=int, default=260, help="grid size of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rtol", type=float, default=1e-10)
+    ap.add_argument("--precond", default="auto", choices=["auto", "jacobi", "two-level"])
+    ap.add_argument("--n-coarse", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "padne_b200" else args.warmup
 
@@ -237,17 +239,20 @@ def main():
         from padne_b200 import dist as pdist
         pdist.init_comm(ctx)                # every pdn_solve below is a collective over all ranks
 
+    precond = {"auto": capi.PRECOND_AUTO, "jacobi": capi.PRECOND_JACOBI, "two-level": capi.PRECOND_TWOLEVEL}[args.precond]
+    skw = dict(n_nodes=fs.n_nodes, rtol=args.rtol, precond=precond, n_coarse=args.n_coarse)
+
     def step_device():
         nnz = ctx.assemble(devt["v_off"], devt["xy"], devt["t_off"], devt["tri"], devt["cond"], fs.N,
                            devt["s_row"], devt["s_col"], devt["s_val"], devt["s_op"])
-        _, info = ctx.solve(devt["rhs"], n_nodes=fs.n_nodes, rtol=args.rtol, out=v_dev)
+        _, info = ctx.solve(devt["rhs"], out=v_dev, **skw)
         return nnz, info
 
     def step_host():
         p = pinned_np
         ctx.assemble(p["v_off"], p["xy"], p["t_off"], p["tri"], p["cond"], fs.N, p["s_row"], p["s_col"],
                      p["s_val"], p["s_op"])
-        _, info = ctx.solve(p["rhs"], n_nodes=fs.n_nodes, rtol=args.rtol, out=v_host_np)
+        _, info = ctx.solve(p["rhs"], out=v_host_np, **skw)
         return info
 
     def timed(fn, steps, warmup):
@@ -309,7 +314,8 @@ def main():
         "config": {"workload": args.config, "grid": args.n or "full", "dof": fs.N,
                    "dof_per_gpu": fs.N // world if partitioned else fs.N, "nnz": int(nnz),
                    "layers": fs.n_mesh, "elements": fs.n_elements, "method": info.method,
-                   "preconditioner": "jacobi", "iterations": info.iterations, "rtol": args.rtol,
+                   "preconditioner": info.precond, "n_coarse": info.n_coarse, "t_coarse_ms": info.t_coarse_ms,
+                   "iterations": info.iterations, "rtol": args.rtol,
                    "rel_residual": info.rel_residual, "residual_norm": info.residual_norm,
                    "t_krylov_ms": info.t_krylov_ms, "t_setup_ms": info.t_setup_ms,
                    "parallelism": ("single GPU" if world == 1 else

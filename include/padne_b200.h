@@ -51,9 +51,12 @@ extern "C" {
 #define PDN_METHOD_BICGSTAB 2
 
 /* preconditioners */
-#define PDN_PRECOND_JACOBI 0
+#define PDN_PRECOND_AUTO 0      /* two-level when the system came from pdn_assemble (coordinates are
+                                   resident) and is symmetric, else Jacobi                              */
 #define PDN_PRECOND_NONE 1
-#define PDN_PRECOND_AMG 2     /* reserved (aggregation multigrid); pdn_solve answers PDN_EUNSUPPORTED */
+#define PDN_PRECOND_AMG 2       /* reserved (multilevel aggregation); pdn_solve answers PDN_EUNSUPPORTED */
+#define PDN_PRECOND_TWOLEVEL 3  /* Jacobi + coarse space of piecewise constants over coordinate bins    */
+#define PDN_PRECOND_JACOBI 4
 
 typedef struct pdn_ctx pdn_ctx;
 
@@ -65,6 +68,8 @@ typedef struct pdn_opts {
     int32_t precond;    /* PDN_PRECOND_*                                                           */
     int32_t check_every;/* iterations per CUDA-graph launch between host convergence polls; 0 -> 32 */
     int64_t n_nodes;    /* voltage unknowns; <0 -> detect (trailing rows without a diagonal entry)  */
+    int32_t n_coarse;   /* target number of aggregates of the two-level preconditioner; 0 -> 1024    */
+    int32_t reserved;
 } pdn_opts;
 
 typedef struct pdn_info {
@@ -80,6 +85,9 @@ typedef struct pdn_info {
     double t_total_ms;
     double spmv_ms;             /* mean duration of one reduced-operator SpMV launch, measured by   */
                                 /* pdn_bench_spmv-style events during the solve (0 if not measured) */
+    int32_t precond;            /* PDN_PRECOND_* actually used                                      */
+    int32_t n_coarse;           /* aggregates of the coarse space (0 without one)                   */
+    double t_coarse_ms;         /* part of t_setup_ms spent building and inverting the coarse matrix */
 } pdn_info;
 
 /* ---- context ------------------------------------------------------------------------------- */

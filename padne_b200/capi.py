@@ -19,7 +19,8 @@ LIB_PATH = os.path.join(_HERE, "_lib", "libpadne_b200.so")
 PDN_OK, PDN_EINVAL, PDN_EDEGENERATE, PDN_ESINGULAR, PDN_ENOTCONVERGED = 0, 1, 2, 3, 4
 PDN_ECUDA, PDN_EUNSUPPORTED, PDN_ENONMANIFOLD, PDN_ENOMEM, PDN_ENOSYSTEM = 5, 6, 7, 8, 9
 METHOD_AUTO, METHOD_PCG, METHOD_BICGSTAB = 0, 1, 2
-PRECOND_JACOBI, PRECOND_NONE, PRECOND_AMG = 0, 1, 2
+PRECOND_AUTO, PRECOND_NONE, PRECOND_AMG, PRECOND_TWOLEVEL, PRECOND_JACOBI = 0, 1, 2, 3, 4
+PRECOND_NAMES = {PRECOND_NONE: "none", PRECOND_TWOLEVEL: "two-level", PRECOND_JACOBI: "jacobi"}
 METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 
 # every symbol include/padne_b200.h declares (tests check that the library exports them all)
@@ -40,7 +41,7 @@ class NotConvergedError(RuntimeError):
 class PdnOpts(ctypes.Structure):
     _fields_ = [("rtol", ctypes.c_double), ("atol", ctypes.c_double), ("max_iter", ctypes.c_int32),
                 ("method", ctypes.c_int32), ("precond", ctypes.c_int32), ("check_every", ctypes.c_int32),
-                ("n_nodes", ctypes.c_int64)]
+                ("n_nodes", ctypes.c_int64), ("n_coarse", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class PdnInfo(ctypes.Structure):
@@ -48,7 +49,8 @@ class PdnInfo(ctypes.Structure):
                 ("n_constraints", ctypes.c_int32), ("rel_residual", ctypes.c_double),
                 ("residual_norm", ctypes.c_double), ("ground_node_current", ctypes.c_double),
                 ("t_setup_ms", ctypes.c_double), ("t_krylov_ms", ctypes.c_double),
-                ("t_total_ms", ctypes.c_double), ("spmv_ms", ctypes.c_double)]
+                ("t_total_ms", ctypes.c_double), ("spmv_ms", ctypes.c_double),
+                ("precond", ctypes.c_int32), ("n_coarse", ctypes.c_int32), ("t_coarse_ms", ctypes.c_double)]
 
 
 @dataclass
@@ -63,6 +65,9 @@ class SolveInfo:
     t_setup_ms: float
     t_krylov_ms: float
     t_total_ms: float
+    precond: str = "jacobi"
+    n_coarse: int = 0
+    t_coarse_ms: float = 0.0
 
 
 _lib = None
@@ -273,7 +278,8 @@ class Context:
 
     # -- kernels (3)+(4) -----------------------------------------------------------------------------
     def solve(self, rhs, n_nodes: int = -1, rtol: float = 0.0, atol: float = 0.0, max_iter: int = 0,
-              method: int = METHOD_AUTO, precond: int = PRECOND_JACOBI, check_every: int = 0, out=None):
+              method: int = METHOD_AUTO, precond: int = PRECOND_AUTO, check_every: int = 0, out=None,
+              n_coarse: int = 0):
         """``solve_system`` (``padne/solver.py:767-780``) on the resident system -> ``(v, SolveInfo)``."""
         dev = _is_device(rhs)
         N, _ = self.shape()
@@ -286,13 +292,14 @@ class Context:
         if rhs.shape[0] != N:
             raise ValueError(f"rhs has {rhs.shape[0]} entries, the system has {N}")
         opts = PdnOpts(rtol=rtol, atol=atol, max_iter=max_iter, method=method, precond=precond,
-                       check_every=check_every, n_nodes=n_nodes)
+                       check_every=check_every, n_nodes=n_nodes, n_coarse=n_coarse)
         info = PdnInfo()
         st = self._lib.pdn_solve(self._ctx, _ptr(rhs), ctypes.byref(opts), _ptr(v), ctypes.byref(info), int(dev))
         self._check(st, "solve")
         return v, SolveInfo(METHOD_NAMES.get(info.method, "?"), info.iterations, info.restarts,
                             info.n_constraints, info.rel_residual, info.residual_norm,
-                            info.ground_node_current, info.t_setup_ms, info.t_krylov_ms, info.t_total_ms)
+                            info.ground_node_current, info.t_setup_ms, info.t_krylov_ms, info.t_total_ms,
+                            PRECOND_NAMES.get(info.precond, "?"), info.n_coarse, info.t_coarse_ms)
 
     def spmv(self, x):
         dev = _is_device(x)

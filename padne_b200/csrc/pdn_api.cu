@@ -189,6 +189,8 @@ int pdn_destroy(pdn_ctx *ctx) {
     pdn_comm_release(ctx);
     ctx->scan_tmp32.release();
     ctx->scan_tmp64.release();
+    ctx->geo_xy_buf.release();
+    ctx->geo_voff.release();
     if (ctx->d_status) cudaFree(ctx->d_status);
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     ctx->L.indptr.release();
@@ -221,6 +223,7 @@ int pdn_assemble(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const doubl
             PDN_FAIL(PDN_EINVAL, "assemble: bad sizes");
         if (n_stamp > 0 && (!s_row || !s_col || !s_val || !s_op)) PDN_FAIL(PDN_EINVAL, "assemble: stamp arrays missing");
         ctx->L.valid = false;
+        ctx->geo_valid = false;
         pdn_assemble_impl(ctx, n_mesh, v_off, xy, t_off, tri, conductance, N, n_stamp, s_row, s_col, s_val,
                           s_op, on_device != 0, nnz_out);
     });
@@ -254,6 +257,7 @@ int pdn_set_csr(pdn_ctx *ctx, int64_t N, int64_t nnz, const int32_t *indptr, con
         cudaMemcpyKind k = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
         CsrDev &L = ctx->L;
         L.valid = false;
+        ctx->geo_valid = false;   // a foreign matrix carries no coordinates: Jacobi only
         L.indptr.reserve((size_t)N + 1);
         L.indices.reserve((size_t)nnz + 1);
         L.data.reserve((size_t)nnz + 1);

@@ -542,5 +542,21 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     L.n = N;
     L.nnz = nnz;
     L.valid = true;
+    // keep the geometry for the solve's coarse space (pdn_coarse.cuh)
+    if (n_v > 0 && n_mesh > 0) {
+        if (on_device) {   // borrowed pointers: take copies
+            ctx->geo_xy_buf.reserve((size_t)n_v * 2);
+            PDN_CUDA(cudaMemcpyAsync(ctx->geo_xy_buf.p, xy, (size_t)n_v * 2 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+            ctx->geo_xy = ctx->geo_xy_buf.p;
+        } else {
+            ctx->geo_xy = d_xy.p;   // the staging copy lives in the context until the next assembly
+        }
+        ctx->geo_voff.reserve((size_t)n_mesh + 1);
+        PDN_CUDA(cudaMemcpyAsync(ctx->geo_voff.p, h_voff.data(), (n_mesh + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        ctx->geo_n_mesh = n_mesh;
+        ctx->geo_n_v = n_v;
+        ctx->geo_valid = true;
+    }
     if (nnz_out) *nnz_out = nnz;
 }

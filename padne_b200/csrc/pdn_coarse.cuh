@@ -1,0 +1,337 @@
+// pdn_coarse.cuh -- kernel (4'): two-level preconditioner  M^-1 = D^-1 + P (P^T A P)^-1 P^T.
+//
+// Jacobi alone needs O(sqrt(N)) iterations on the plane Laplacians (4 204 at 1M DOF).  The second
+// level is a coarse space of piecewise constants over AGGREGATES: the vertices of every mesh are
+// binned on a uniform grid of their coordinates (pdn_assemble keeps xy resident), internal network
+// nodes get aggregates of their own, rows eliminated by the constraints get none.  About a thousand
+// aggregates remove the long-wavelength error the Jacobi sweep cannot see; the iteration count then
+// depends on the bin size in mesh cells, not on N (measured on the CPU model: 1 474 -> 381 / 211 / 130
+// at 32 / 16 / 8 cells per bin).
+//
+//   setup   aggregate ids (bins -> compact ids by a scan)
+//           A_c = P^T A P accumulated in 64-bit FIXED POINT: integer atomics are associative, so the
+//           coarse matrix -- and with it the whole solve -- stays bit-identical run to run
+//           A_c^-1 by a cooperative blocked Gauss-Jordan: every CTA keeps its rows of the matrix in
+//           shared memory for the whole inversion, one grid barrier per block of pivots
+//   apply   r_c = P^T r  is fused into the PCG vector update (fixed point again, scaled by ||r||)
+//           x_c = A_c^-1 r_c   dense mat-vec, one warp per row
+//           z   = D^-1 r + P x_c
+//
+// Included by pdn_kernels.cuh (namespace pdnk).
+#pragma once
+
+constexpr int CO_MAX = 1776;          // largest coarse space: 12 rows x 1776 doubles per CTA = 170 KB
+constexpr int CO_BLK = 256;
+constexpr double CO_RFIX = 1099511627776.0;   // 2^40: fixed-point steps per ||r|| in the restriction
+
+struct CoarseGeom {
+    int n_mesh;
+    int64_t n_v;               // mesh vertices (old numbering: [0, n_v) have coordinates)
+    double x0, y0, inv_h;      // bin = floor((x - x0) * inv_h)
+    int32_t nbx, nby;          // bins per mesh
+    int32_t n_bins;            // n_mesh * nbx * nby
+    int32_t node_group;        // internal nodes per aggregate
+};
+
+// per-block bounding box partials: out[4*b + {0,1,2,3}] = min x, min y, max x, max y
+__global__ void __launch_bounds__(CO_BLK) bbox_kernel(int64_t n_v, const double2 *__restrict__ xy, double *__restrict__ out) {
+    __shared__ double sm[4][CO_BLK / 32];
+    double v[4] = {1e300, 1e300, -1e300, -1e300};
+    for (int64_t i = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; i < n_v; i += (int64_t)gridDim.x * CO_BLK) {
+        const double2 p = xy[i];
+        v[0] = fmin(v[0], p.x); v[1] = fmin(v[1], p.y); v[2] = fmax(v[2], p.x); v[3] = fmax(v[3], p.y);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double t = __shfl_down_sync(0xffffffffu, v[a], o);
+            v[a] = a < 2 ? fmin(v[a], t) : fmax(v[a], t);
+        }
+        if (lane == 0) sm[a][warp] = v[a];
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        const int a = threadIdx.x;
+        double r = sm[a][0];
+        for (int k = 1; k < CO_BLK / 32; k++) r = a < 2 ? fmin(r, sm[a][k]) : fmax(r, sm[a][k]);
+        out[4 * blockIdx.x + a] = r;
+    }
+}
+
+// raw aggregate id of every reduced row (permuted numbering); -1 for rows the constraints eliminated
+__global__ void __launch_bounds__(CO_BLK) agg_raw_kernel(int64_t n, CoarseGeom g, const int64_t *__restrict__ v_off,
+                                                         const double2 *__restrict__ xy,
+                                                         const int32_t *__restrict__ perm,
+                                                         const int32_t *__restrict__ map, int32_t *__restrict__ raw,
+                                                         int32_t *__restrict__ used) {
+    for (int64_t r = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; r < n; r += (int64_t)gridDim.x * CO_BLK) {
+        const int32_t i = perm[r];
+        int32_t a = -1;
+        if (map[i] == i) {
+            if (i < g.n_v) {
+                int lo = 0, hi = g.n_mesh;          // largest m with v_off[m] <= i
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (v_off[mid] <= i) lo = mid; else hi = mid;
+                }
+                const double2 p = xy[i];
+                int bx = (int)floor((p.x - g.x0) * g.inv_h), by = (int)floor((p.y - g.y0) * g.inv_h);
+                bx = bx < 0 ? 0 : (bx >= g.nbx ? g.nbx - 1 : bx);
+                by = by < 0 ? 0 : (by >= g.nby ? g.nby - 1 : by);
+                a = (lo * g.nby + by) * g.nbx + bx;
+            } else {
+                a = g.n_bins + (int32_t)((i - g.n_v) / g.node_group);
+            }
+            used[a] = 1;
+        }
+        raw[r] = a;
+    }
+}
+
+__global__ void __launch_bounds__(CO_BLK) agg_final_kernel(int64_t n, const int32_t *__restrict__ cid, int32_t *__restrict__ agg) {
+    for (int64_t r = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; r < n; r += (int64_t)gridDim.x * CO_BLK) {
+        const int32_t a = agg[r];
+        agg[r] = a < 0 ? -1 : cid[a];
+    }
+}
+
+// largest Jacobi diagonal (= 1 / smallest dinv): the fixed-point scale of A_c
+__global__ void __launch_bounds__(CO_BLK) min_kernel(int64_t n, const double *__restrict__ v, double *__restrict__ out) {
+    __shared__ double sm[CO_BLK / 32];
+    double m = 1e300;
+    for (int64_t i = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * CO_BLK) m = fmin(m, v[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmin(m, __shfl_down_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < CO_BLK / 32; k++) m = fmin(m, sm[k]);
+        out[blockIdx.x] = m;
+    }
+}
+
+// one 64-bit integer atomic per distinct key in the warp (lanes with key < 0 contribute nothing)
+__device__ __forceinline__ void warp_add_by_key(long long key, long long val, unsigned long long *table) {
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(peers) - 1;
+    long long sum = 0;
+    for (int l = 0; l < 32; l++) {
+        const long long v = __shfl_sync(0xffffffffu, val, l);
+        if ((peers >> l) & 1u) sum += v;
+    }
+    if (lane == leader && key >= 0 && sum != 0) atomicAdd(&table[key], (unsigned long long)sum);
+}
+
+// A_c[I][J] += a_ij (fixed point) over the SELL part (one warp per slice) ...
+__global__ void __launch_bounds__(CO_BLK) coarse_accum_kernel(SellOp A, int64_t n_slices, const int32_t *__restrict__ agg,
+                                                              int32_t nc, double fix, unsigned long long *__restrict__ acc) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * CO_BLK + threadIdx.x) >> 5;
+    const int64_t n_warp = ((int64_t)gridDim.x * CO_BLK) >> 5;
+    for (int64_t s = warp; s < n_slices; s += n_warp) {
+        const int64_t r = s * SELL_C + lane;
+        const int32_t off = A.soff[s], w = (A.soff[s + 1] - off) >> 5;
+        const int32_t I = r < A.n ? agg[r] : -1;
+        for (int32_t k = 0; k < w; k++) {
+            const int32_t c = A.ci[off + k * SELL_C + lane];
+            const double v = A.va[off + k * SELL_C + lane];
+            const int32_t J = I >= 0 && v != 0.0 ? agg[c] : -1;
+            const long long key = J >= 0 ? (long long)I * nc + J : -1;
+            warp_add_by_key(key, llrint(v * fix), acc);
+        }
+    }
+}
+// ... and over the override rows (one thread per row, plain atomics: there are few)
+__global__ void __launch_bounds__(CO_BLK) coarse_accum_special_kernel(SellOp A, const int32_t *__restrict__ agg, int32_t nc,
+                                                                      double fix, unsigned long long *__restrict__ acc) {
+    for (int32_t t = blockIdx.x * CO_BLK + threadIdx.x; t < A.n_special; t += gridDim.x * CO_BLK) {
+        const int32_t I = agg[A.sp_row[t]];
+        if (I < 0) continue;
+        for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) {
+            const int32_t J = agg[A.sp_ci[q]];
+            if (J >= 0) atomicAdd(&acc[(long long)I * nc + J], (unsigned long long)llrint(A.sp_va[q] * fix));
+        }
+    }
+}
+
+// fixed point -> double, symmetrised
+__global__ void __launch_bounds__(CO_BLK) coarse_convert_kernel(int32_t nc, double inv_fix, const long long *__restrict__ acc,
+                                                                double *__restrict__ Ac) {
+    const int64_t tot = (int64_t)nc * nc;
+    for (int64_t e = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; e < tot; e += (int64_t)gridDim.x * CO_BLK) {
+        const int32_t i = (int32_t)(e / nc), j = (int32_t)(e - (int64_t)i * nc);
+        Ac[e] = 0.5 * ((double)acc[e] + (double)acc[(int64_t)j * nc + i]) * inv_fix;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// in-place inverse of the SPD coarse matrix: cooperative blocked Gauss-Jordan (no pivoting).
+// CTA b owns rows [b*R, (b+1)*R) and keeps them in shared memory.  Block step b (the sweep operator over
+// the pivot block K = rows of CTA b): the owner sweeps its own rows (R local steps), publishes them,
+// one grid barrier, every other CTA applies  A_i,j <- (j in K ? 0 : A_i,j) - sum_q A_i,K[q] * piv_q,j.
+// Launched cooperatively (all CTAs co-resident); status[0] != 0 on a non-positive pivot / timeout.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool grid_barrier(unsigned int *counter, unsigned int target, int32_t *status) {
+    __syncthreads();
+    __shared__ int ok;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        const long long t0 = clock64();
+        int good = 1;
+        while (true) {
+            unsigned int v;
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter));
+            if (v >= target) break;
+            if (clock64() - t0 > 4000000000LL) { good = 0; atomicExch(&status[0], PDN_ECUDA); break; }   // ~2 s
+        }
+        ok = good;
+        __threadfence();
+    }
+    __syncthreads();
+    return ok != 0;
+}
+
+__global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, int32_t R, double *__restrict__ A,
+                                                                  double *__restrict__ piv /*[2][R * nc]*/,
+                                                                  unsigned int *counter, int32_t *status) {
+    extern __shared__ double rows[];                 // [R][nc]
+    __shared__ double cs[16][16];                    // multipliers (R <= 16)
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int r0 = b * R;
+    const int nr = r0 >= nc ? 0 : (r0 + R <= nc ? R : nc - r0);
+    for (int e = tid; e < nr * nc; e += CO_BLK) rows[e] = A[(size_t)r0 * nc + e];
+    __syncthreads();
+    const int n_blk = (nc + R - 1) / R;
+    unsigned int target = 0;
+    for (int kb = 0; kb < n_blk; kb++) {
+        const int k0 = kb * R, nk = k0 + R <= nc ? R : nc - k0;
+        double *pb = piv + (size_t)(kb & 1) * R * nc;      // double-buffered: one barrier per block step
+        if (kb == b) {
+            // sweep my own rows over the pivots k0 .. k0+nk-1
+            for (int q = 0; q < nk; q++) {
+                const int k = k0 + q;
+                if (tid < nk) cs[0][tid] = rows[tid * nc + k];
+                __syncthreads();
+                const double p = cs[0][q];
+                if (!(p > 0.0) && tid == 0) atomicExch(&status[0], PDN_ESINGULAR);
+                const double ip = 1.0 / p;
+                for (int j = tid; j < nc; j += CO_BLK) {
+                    const double pr = (j == k ? 1.0 : rows[q * nc + j]) * ip;
+                    rows[q * nc + j] = pr;
+                    for (int i = 0; i < nk; i++) {
+                        if (i == q) continue;
+                        const double cur = j == k ? 0.0 : rows[i * nc + j];
+                        rows[i * nc + j] = cur - cs[0][i] * pr;
+                    }
+                }
+                __syncthreads();
+            }
+            for (int e = tid; e < nk * nc; e += CO_BLK) pb[e] = rows[e];
+        }
+        target += gridDim.x;
+        if (!grid_barrier(counter, target, status)) return;
+        if (kb != b && nr > 0) {
+            // A_i,j <- (j in K ? 0 : A_i,j) - sum_q A_i,K[q] (old) * piv_q,j
+            for (int e = tid; e < nr * nk; e += CO_BLK) cs[e / nk][e % nk] = rows[(e / nk) * nc + k0 + (e % nk)];
+            __syncthreads();
+            for (int j = tid; j < nc; j += CO_BLK) {
+                double pj[16];
+#pragma unroll
+                for (int q = 0; q < 16; q++) pj[q] = q < nk ? __ldcg(&pb[q * nc + j]) : 0.0;
+                const bool in_k = j >= k0 && j < k0 + nk;
+                for (int i = 0; i < nr; i++) {
+                    double sacc = in_k ? 0.0 : rows[i * nc + j];
+#pragma unroll
+                    for (int q = 0; q < 16; q++)
+                        if (q < nk) sacc -= cs[i][q] * pj[q];
+                    rows[i * nc + j] = sacc;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    for (int e = tid; e < nr * nc; e += CO_BLK) A[(size_t)r0 * nc + e] = rows[e];
+}
+
+// ------------------------------------------------------------------------------------------------
+// apply
+// ------------------------------------------------------------------------------------------------
+// x_c = A_c^-1 r_c  (r_c arrives in fixed point, parity = iteration & 1); the other parity's
+// accumulator is cleared for the next restriction.  CTA b owns CO_RB consecutive rows at a time: every
+// thread issues the loads of its columns for ALL of them before the first use (the matrix is
+// L2-resident, the kernel is latency-bound), then one block reduction of CO_RB sums in a fixed order.
+constexpr int CO_RB = 8;
+__global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const double *__restrict__ Ainv, const Scal *__restrict__ sc,
+                                                              long long *__restrict__ rc_fix, double *__restrict__ xc) {
+    __shared__ double rcd[CO_MAX];
+    __shared__ double red[CO_RB][CO_BLK / 32];
+    if (sc->done) return;
+    const int par = sc->iter & 1;
+    const long long *__restrict__ rc = rc_fix + (size_t)par * nc;
+    long long *__restrict__ other = rc_fix + (size_t)(par ^ 1) * nc;
+    const double scale = sqrt(fmax(sc->rr, 1e-300)) / CO_RFIX;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int j = tid; j < nc; j += CO_BLK) rcd[j] = (double)rc[j] * scale;
+    __syncthreads();
+    for (int row0 = blockIdx.x * CO_RB; row0 < nc; row0 += gridDim.x * CO_RB) {
+        double acc[CO_RB];
+#pragma unroll
+        for (int q = 0; q < CO_RB; q++) acc[q] = 0.0;
+        for (int j = tid; j < nc; j += CO_BLK) {
+            double a[CO_RB];
+#pragma unroll
+            for (int q = 0; q < CO_RB; q++) a[q] = row0 + q < nc ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.0;
+            const double x = rcd[j];
+#pragma unroll
+            for (int q = 0; q < CO_RB; q++) acc[q] = fma(a[q], x, acc[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < CO_RB; q++) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_down_sync(0xffffffffu, acc[q], o);
+            if (lane == 0) red[q][warp] = acc[q];
+        }
+        __syncthreads();
+        if (tid < CO_RB && row0 + tid < nc) {
+            double sum = 0.0;
+            for (int k = 0; k < CO_BLK / 32; k++) sum += red[tid][k];
+            xc[row0 + tid] = sum;
+            other[row0 + tid] = 0;
+        }
+        __syncthreads();
+    }
+}
+
+// z = D^-1 r + P x_c  over the rows [r0, n)
+__global__ void __launch_bounds__(CO_BLK) coarse_z_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
+                                                          const double *__restrict__ dinv, const double *__restrict__ r,
+                                                          const int32_t *__restrict__ agg, const double *__restrict__ xc,
+                                                          double *__restrict__ z) {
+    if (sc->done) return;
+    for (int64_t i = r0 + (int64_t)blockIdx.x * CO_BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * CO_BLK) {
+        const int32_t a = agg[i];
+        z[i] = dinv[i] * r[i] + (a >= 0 ? __ldg(&xc[a]) : 0.0);
+    }
+}
+
+// restriction of one residual entry into the fixed-point accumulator (called by the update kernels,
+// whole warps converged).  Lanes with the same aggregate are summed with three redux.sync over 19-bit
+// limbs of the biased value (|value| < 2^56), one integer atomic per distinct aggregate in the warp.
+__device__ __forceinline__ void restrict_add(double ri, int32_t a, double fix, unsigned long long *rc) {
+    const double lim = 72057594037927935.0;   // 2^56 - 1
+    double q = ri * fix;
+    q = q > lim ? lim : (q < -lim ? -lim : q);
+    const unsigned long long u = (unsigned long long)(llrint(q) + (1LL << 56));
+    const unsigned peers = __match_any_sync(0xffffffffu, a);
+    const unsigned s0 = __reduce_add_sync(peers, (unsigned)(u & 0x7ffffu));
+    const unsigned s1 = __reduce_add_sync(peers, (unsigned)((u >> 19) & 0x7ffffu));
+    const unsigned s2 = __reduce_add_sync(peers, (unsigned)(u >> 38));
+    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && a >= 0) {
+        const long long sum = (long long)s0 + ((long long)s1 << 19) + ((long long)s2 << 38) - ((long long)__popc(peers) << 56);
+        if (sum != 0) atomicAdd(&rc[a], (unsigned long long)sum);
+    }
+}

@@ -110,6 +110,13 @@ struct pdn_ctx {
     SolveWork *solve = nullptr;
     AssembleWork *asmw = nullptr;
     PdnComm *comm = nullptr;      // set by pdn_comm_init (one rank per GPU); null = single GPU
+    // geometry of the resident system (kept by pdn_assemble for the coarse space of the solve)
+    bool geo_valid = false;
+    const double *geo_xy = nullptr;   // [geo_n_v, 2] device pointer (into asmw or geo_xy_buf)
+    DevBuf<double> geo_xy_buf;
+    DevBuf<int64_t> geo_voff;         // [geo_n_mesh + 1] device copy
+    int geo_n_mesh = 0;
+    int64_t geo_n_v = 0;
     DevBuf<int32_t> scan_tmp32;   // tile totals of the device-wide scans
     DevBuf<int64_t> scan_tmp64;
 };
@@ -184,6 +191,7 @@ int pdn_comm_rank(const pdn_ctx *ctx);
 int pdn_comm_world(const pdn_ctx *ctx);
 void pdn_comm_release(pdn_ctx *ctx);
 void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count);
+void pdn_comm_allreduce_sum_i64(pdn_ctx *ctx, long long *buf, int count);
 void pdn_comm_allgatherv(pdn_ctx *ctx, double *vec, const int64_t *begin);
 void pdn_comm_exchange(pdn_ctx *ctx, const double *sendbuf, const int32_t *send_off, const int32_t *send_cnt,
                        double *recvbuf, const int32_t *recv_off, const int32_t *recv_cnt);

@@ -111,6 +111,7 @@ __device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partial
 // ------------------------------------------------------------------------------------------------
 #include "pdn_spmv.cuh"
 #include "pdn_sell.cuh"
+#include "pdn_coarse.cuh"
 
 // scalar recurrences of the BiCGSTAB vector kernels (one thread, after the grid-wide reduction)
 __device__ __forceinline__ void bicg_x_finalize(const double (&acc)[3], Scal *sc) {
@@ -151,33 +152,57 @@ __global__ void scalar_kernel(Scal *sc, double *out) {
 // rank owns (r0 = 0 and n = all rows on a single GPU)
 // ------------------------------------------------------------------------------------------------
 // Chronopoulos-Gear update:  p = z + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  z = dinv r
+// TL (two-level preconditioner): z is produced later by coarse_z_kernel; here the new residual is
+// restricted onto the aggregates, r_c[agg] += r (fixed point, pdn_coarse.cuh).
+template <bool TL>
 __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                         const double *__restrict__ dinv,
                                                         const double *__restrict__ w, double *__restrict__ z,
                                                         double *__restrict__ p, double *__restrict__ s,
-                                                        double *__restrict__ x, double *__restrict__ r) {
+                                                        double *__restrict__ x, double *__restrict__ r,
+                                                        const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
     if (sc->done) return;
     const double alpha = sc->alpha, beta = sc->beta;
-    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
-        const double pi = z[i] + beta * p[i];
-        const double si = w[i] + beta * s[i];
-        const double ri = r[i] - alpha * si;
-        p[i] = pi;
-        s[i] = si;
-        x[i] += alpha * pi;
-        r[i] = ri;
-        z[i] = dinv[i] * ri;
+    const double fix = TL ? CO_RFIX / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
+    unsigned long long *rc = TL ? reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc : nullptr;
+    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool act = i < n;
+        double ri = 0.0;
+        if (act) {
+            const double pi = z[i] + beta * p[i];
+            const double si = w[i] + beta * s[i];
+            ri = r[i] - alpha * si;
+            p[i] = pi;
+            s[i] = si;
+            x[i] += alpha * pi;
+            r[i] = ri;
+            if (!TL) z[i] = dinv[i] * ri;
+        }
+        if (TL) restrict_add(ri, act ? agg[i] : -1, fix, rc);
     }
 }
 
-// r = b (x = 0 start) or given r;  z = dinv r;  p = s = 0
-__global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, const double *__restrict__ dinv,
+// start / restart from the residual r:  z = dinv r (or its restriction, TL);  p = s = 0
+template <bool TL>
+__global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
+                                                      const double *__restrict__ dinv,
                                                       const double *__restrict__ r, double *__restrict__ z,
-                                                      double *__restrict__ p, double *__restrict__ s) {
-    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
-        z[i] = dinv[i] * r[i];
-        p[i] = 0.0;
-        s[i] = 0.0;
+                                                      double *__restrict__ p, double *__restrict__ s,
+                                                      const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
+    const double fix = TL ? CO_RFIX / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
+    unsigned long long *rc = TL ? reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc : nullptr;
+    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool act = i < n;
+        double ri = 0.0;
+        if (act) {
+            ri = r[i];
+            if (!TL) z[i] = dinv[i] * ri;
+            p[i] = 0.0;
+            s[i] = 0.0;
+        }
+        if (TL) restrict_add(ri, act ? agg[i] : -1, fix, rc);
     }
 }
 

@@ -20,7 +20,7 @@ typedef struct ncclComm *ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 constexpr int kNcclSuccess = 0;
 constexpr int kNcclSum = 0;
-constexpr int kNcclInt32 = 2;     // ncclInt32
+constexpr int kNcclInt64 = 4;     // ncclInt64
 constexpr int kNcclFloat64 = 8;   // ncclFloat64
 
 struct NcclApi {
@@ -92,6 +92,11 @@ void pdn_comm_release(pdn_ctx *ctx) {
 // in-place sum of `count` doubles on the context stream
 void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count) {
     PDN_NCCL(nccl().AllReduce(buf, buf, (size_t)count, kNcclFloat64, kNcclSum, ctx->comm->comm, ctx->stream));
+}
+
+// in-place sum of 64-bit integers (the fixed-point coarse residual: exact, order-independent)
+void pdn_comm_allreduce_sum_i64(pdn_ctx *ctx, long long *buf, int count) {
+    PDN_NCCL(nccl().AllReduce(buf, buf, (size_t)count, kNcclInt64, kNcclSum, ctx->comm->comm, ctx->stream));
 }
 
 // vec[begin[k] .. begin[k+1]) is broadcast from rank k, for every k (an all-gather with ragged slices)

@@ -151,6 +151,14 @@ struct SolveWork {
     DevBuf<uint8_t> special;
     DevBuf<double> s_va, dinv, sp_va, off, tmp_f64a, tmp_f64b;
     int32_t n_special = 0;
+    // two-level preconditioner (pdn_coarse.cuh)
+    bool two_level = false;
+    int32_t nc = 0;
+    float coarse_ms = 0.f;
+    DevBuf<int32_t> agg, co_used, co_cid;
+    DevBuf<long long> co_acc, rc_fix;
+    DevBuf<double> co_A, co_piv, xc, co_tmp;
+    DevBuf<unsigned int> co_counter;
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
     DevBuf<double> partials;
@@ -496,6 +504,7 @@ void reset_scal(pdn_ctx *ctx, SolveWork *w, double tol2, double bnorm2, int max_
     Scal h{};
     h.tol2 = tol2;
     h.bnorm2 = bnorm2;
+    h.rr = bnorm2;     // r = b at the start: the scale of the first fixed-point restriction
     h.first = 1;
     h.max_iter = max_iter;
     h.omega = 1.0;
@@ -520,12 +529,30 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w) {
 }
 
 // one iteration = SpMV with fused dots (+ halo exchange and all-reduce on several GPUs) + vector update
+// two-level: x_c = A_c^-1 r_c, z = D^-1 r + P x_c  (r_c was accumulated by the update / init kernel)
+void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid) {
+    if (is_dist(ctx)) {   // every rank restricted its own rows: exact integer sum, identical everywhere
+        // both parities are reduced (2 nc values): the idle one is all zeros
+        pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
+    }
+    const int cgrid = std::max(1, std::min(2 * ctx->n_sm, (w->nc + CO_RB - 1) / CO_RB));
+    PDN_LAUNCH(ctx, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_A.p, w->d_sc, w->rc_fix.p, w->xc.p);
+    PDN_LAUNCH(ctx, coarse_z_kernel, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, w->r.p, w->agg.p,
+               w->xc.p, w->z.p);
+}
+
 void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     const int64_t r0 = w->row_begin, r1 = w->row_end;
     halo_exchange(ctx, w, w->z.p);
     launch_sell<CG>(ctx, w, w->z.p, w->w.p, w->r.p);
-    PDN_LAUNCH(ctx, cg_update_kernel, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
-               w->x.p, w->r.p);
+    if (w->two_level) {
+        PDN_LAUNCH(ctx, cg_update_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
+                   w->x.p, w->r.p, w->agg.p, w->rc_fix.p, w->nc);
+        enqueue_coarse_correction(ctx, w, vgrid);
+    } else {
+        PDN_LAUNCH(ctx, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
+                   w->x.p, w->r.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
+    }
 }
 
 void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
@@ -618,7 +645,8 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         PDN_CUDA(cudaGraphInstantiate(&exec, graph, 0));
         ctx->launches = launches_before;  // capture is not execution
     };
-    const int per_iter = (method == PDN_METHOD_PCG ? 2 : 5) + (dist ? (method == PDN_METHOD_PCG ? 3 : 7) : 0);
+    const int per_iter = (method == PDN_METHOD_PCG ? 2 : 5) + (dist ? (method == PDN_METHOD_PCG ? 3 : 7) : 0) +
+                         (method == PDN_METHOD_PCG && w->two_level ? 2 : 0);
     build_graph();
 
     auto cleanup = [&]() {
@@ -633,8 +661,14 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         double best_rr = -1.0;
         for (int attempt = 0;; attempt++) {
             // start / restart from the current residual r
-            if (method == PDN_METHOD_PCG) {
-                PDN_LAUNCH(ctx, cg_init_kernel, vgrid, RPB, 0, r0, r1, w->dinv.p, w->r.p, w->z.p, w->p.p, w->s.p);
+            if (method == PDN_METHOD_PCG && w->two_level) {
+                PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
+                PDN_LAUNCH(ctx, cg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
+                           w->s.p, w->agg.p, w->rc_fix.p, w->nc);
+                enqueue_coarse_correction(ctx, w, vgrid);
+            } else if (method == PDN_METHOD_PCG) {
+                PDN_LAUNCH(ctx, cg_init_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
+                           w->s.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
             } else if (dist) {
                 PDN_LAUNCH(ctx, bicg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->rhat.p,
                            w->p.p, w->ph.p, w->partials.p);
@@ -827,6 +861,132 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     upload(ctx, h.recv_idx, recv_idx);
     h.sendbuf.reserve((size_t)h.n_send + 1);
     h.recvbuf.reserve((size_t)h.n_recv + 1);
+}
+
+// ------------------------------------------------------------------------------------------------
+// two-level preconditioner: aggregates, coarse matrix, its inverse (kernels in pdn_coarse.cuh).
+// Returns false (and leaves Jacobi in place) when no useful coarse space can be built.
+// ------------------------------------------------------------------------------------------------
+static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_entries) {
+    cudaStream_t st = ctx->stream;
+    const int64_t n = w->n;
+    w->two_level = false;
+    w->nc = 0;
+    if (!ctx->geo_valid || ctx->geo_n_v <= 0 || ctx->geo_n_v > n) return false;
+    if (target <= 0) target = 1024;
+    if (target > CO_MAX) target = CO_MAX;
+    if (target > n / 16) target = (int32_t)(n / 16);     // tiny systems: keep >= 16 rows per aggregate
+    if (target < 4) return false;
+
+    // bounding box of the vertices
+    const int bgrid = pdn_grid(ctx, ctx->geo_n_v, CO_BLK, 4);
+    w->co_tmp.reserve((size_t)4 * bgrid + 2048);
+    PDN_LAUNCH(ctx, bbox_kernel, bgrid, CO_BLK, 0, ctx->geo_n_v, (const double2 *)ctx->geo_xy, w->co_tmp.p);
+    std::vector<double> hb((size_t)4 * bgrid);
+    PDN_CUDA(cudaMemcpyAsync(hb.data(), w->co_tmp.p, hb.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+    for (int b = 0; b < bgrid; b++) {
+        x0 = std::min(x0, hb[4 * b]); y0 = std::min(y0, hb[4 * b + 1]);
+        x1 = std::max(x1, hb[4 * b + 2]); y1 = std::max(y1, hb[4 * b + 3]);
+    }
+    if (!(x1 >= x0) || !(y1 >= y0)) return false;
+
+    // bins: equal squares, about `target` aggregates in total
+    CoarseGeom g{};
+    g.n_mesh = ctx->geo_n_mesh;
+    g.n_v = ctx->geo_n_v;
+    const int64_t n_internal = n - ctx->geo_n_v;
+    g.node_group = n_internal > 256 ? (int32_t)((n_internal + 255) / 256) : 1;
+    const int32_t node_aggs = (int32_t)((n_internal + g.node_group - 1) / g.node_group);
+    const double W = std::max(x1 - x0, 1e-12), Ht = std::max(y1 - y0, 1e-12);
+    double bins_per_mesh = std::max(1.0, (double)(target - node_aggs) / g.n_mesh);
+    double H = sqrt(W * Ht / bins_per_mesh);
+    for (int guard = 0; guard < 200; guard++) {
+        g.nbx = std::max(1, (int)ceil(W / H));
+        g.nby = std::max(1, (int)ceil(Ht / H));
+        if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs <= std::max<int64_t>(target, 4)) break;
+        H *= 1.05;
+    }
+    if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs > CO_MAX) return false;
+    g.x0 = x0; g.y0 = y0; g.inv_h = 1.0 / H;
+    g.n_bins = g.n_mesh * g.nbx * g.nby;
+    const int32_t n_raw = g.n_bins + node_aggs;
+
+    // aggregate ids: raw bin -> compact id over the non-empty bins
+    w->agg.reserve((size_t)n);
+    w->co_used.reserve((size_t)n_raw + 1);
+    w->co_cid.reserve((size_t)n_raw + 1);
+    PDN_CUDA(cudaMemsetAsync(w->co_used.p, 0, ((size_t)n_raw + 1) * sizeof(int32_t), st));
+    PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, g, ctx->geo_voff.p,
+               (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, w->agg.p, w->co_used.p);
+    pdn_exclusive_scan_i32(ctx, w->co_used.p, n_raw, w->co_cid.p);
+    int32_t nc = 0;
+    PDN_CUDA(cudaMemcpyAsync(&nc, w->co_cid.p + n_raw, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    if (nc < 2 || nc > CO_MAX) return false;
+    PDN_LAUNCH(ctx, agg_final_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->co_cid.p, w->agg.p);
+
+    // fixed-point scale of A_c: |sum| <= entries * largest diagonal must stay below 2^62
+    const int mgrid = pdn_grid(ctx, n, CO_BLK, 4);
+    PDN_LAUNCH(ctx, min_kernel, mgrid, CO_BLK, 0, n, w->dinv.p, w->co_tmp.p);
+    std::vector<double> hm((size_t)mgrid);
+    PDN_CUDA(cudaMemcpyAsync(hm.data(), w->co_tmp.p, hm.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    double dmin = 1e300;
+    for (double v : hm) dmin = std::min(dmin, v);
+    if (!(dmin > 0.0) || !(dmin < 1e300)) return false;
+    const double amax = 1.0 / dmin;
+    const double fix = exp2(floor(log2(4.0e18 / ((double)std::max<int64_t>(n_entries, 1) * amax))));
+
+    const size_t nc2 = (size_t)nc * nc;
+    w->co_acc.reserve(nc2);
+    w->co_A.reserve(nc2);
+    PDN_CUDA(cudaMemsetAsync(w->co_acc.p, 0, nc2 * sizeof(long long), st));
+    PDN_LAUNCH(ctx, coarse_accum_kernel, pdn_grid(ctx, w->n_slices * 32, CO_BLK, 8), CO_BLK, 0, w->A, w->n_slices, w->agg.p,
+               nc, fix, (unsigned long long *)w->co_acc.p);
+    if (w->A.n_special > 0)
+        PDN_LAUNCH(ctx, coarse_accum_special_kernel, pdn_blocks(w->A.n_special, CO_BLK), CO_BLK, 0, w->A, w->agg.p, nc, fix,
+                   (unsigned long long *)w->co_acc.p);
+    PDN_LAUNCH(ctx, coarse_convert_kernel, pdn_grid(ctx, (int64_t)nc2, CO_BLK, 8), CO_BLK, 0, nc, 1.0 / fix, w->co_acc.p,
+               w->co_A.p);
+
+    // inverse: cooperative blocked Gauss-Jordan, rows of the matrix resident in shared memory
+    const int32_t R = (nc + ctx->n_sm - 1) / ctx->n_sm;
+    if (R > 16) return false;
+    const int grid = (nc + R - 1) / R;
+    const size_t smem = (size_t)R * nc * sizeof(double);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        PDN_CUDA(cudaFuncSetAttribute(coarse_invert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(220 * 1024)));
+        smem_set = 220 * 1024;
+    }
+    if (smem > 220 * 1024) return false;
+    w->co_piv.reserve((size_t)2 * R * nc);
+    w->co_counter.reserve(4);
+    PDN_CUDA(cudaMemsetAsync(w->co_counter.p, 0, 4 * sizeof(unsigned int), st));
+    pdn_status_reset(ctx);
+    {
+        int32_t nc_arg = nc, R_arg = R;
+        double *A_arg = w->co_A.p, *piv_arg = w->co_piv.p;
+        unsigned int *cnt_arg = w->co_counter.p;
+        int32_t *st_arg = ctx->d_status;
+        void *args[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg};
+        PDN_CUDA(cudaLaunchCooperativeKernel((void *)coarse_invert_kernel, dim3(grid), dim3(CO_BLK), args, smem, st));
+        ctx->launches++;
+    }
+    int64_t detail = 0;
+    const int stt = pdn_status_fetch(ctx, &detail);
+    if (stt != 0) {   // not positive definite (or a stuck barrier): fall back to Jacobi, loudly in last_error
+        pdn_status_reset(ctx);
+        ctx->last_error = std::string("coarse matrix inversion failed (") + pdn_strerror(stt) + "): Jacobi only";
+        return false;
+    }
+    w->rc_fix.reserve((size_t)2 * nc);
+    w->xc.reserve((size_t)nc);
+    w->nc = nc;
+    w->two_level = true;
+    return true;
 }
 
 void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, double *v_out, pdn_info *info,
@@ -1102,6 +1262,37 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     }
     w->have_operator = true;
 
+    // second level of the preconditioner (symmetric systems assembled from meshes)
+    w->two_level = false;
+    w->nc = 0;
+    w->coarse_ms = 0.f;
+    {
+        const bool want = opts.precond == PDN_PRECOND_TWOLEVEL || (opts.precond == PDN_PRECOND_AUTO && n >= 1024);
+        if (opts.precond == PDN_PRECOND_TWOLEVEL && (method != PDN_METHOD_PCG || !ctx->geo_valid))
+            PDN_FAIL(PDN_EUNSUPPORTED, "solve: the two-level preconditioner needs a symmetric system assembled by pdn_assemble");
+        if (want && method == PDN_METHOD_PCG && ctx->geo_valid) {
+            cudaEvent_t c0, c1;
+            PDN_CUDA(cudaEventCreate(&c0));
+            PDN_CUDA(cudaEventCreate(&c1));
+            PDN_CUDA(cudaEventRecord(c0, st));
+            bool ok = false;
+            try {
+                ok = build_coarse(ctx, w, opts.n_coarse, (int64_t)sell_total + (int64_t)r_ci.size());
+            } catch (...) {
+                cudaEventDestroy(c0);
+                cudaEventDestroy(c1);
+                throw;
+            }
+            PDN_CUDA(cudaEventRecord(c1, st));
+            PDN_CUDA(cudaEventSynchronize(c1));
+            cudaEventElapsedTime(&w->coarse_ms, c0, c1);
+            cudaEventDestroy(c0);
+            cudaEventDestroy(c1);
+            if (!ok && opts.precond == PDN_PRECOND_TWOLEVEL)
+                PDN_FAIL(PDN_EUNSUPPORTED, "solve: no coarse space could be built (%s)", ctx->last_error.c_str());
+        }
+    }
+
     // vectors
     w->x.reserve((size_t)n); w->r.reserve((size_t)n); w->z.reserve((size_t)n); w->p.reserve((size_t)n);
     w->s.reserve((size_t)n); w->w.reserve((size_t)n);
@@ -1161,6 +1352,10 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         info->t_krylov_ms = kr.ms;
         info->t_total_ms = t_total;
         info->spmv_ms = 0.0;
+        info->precond = w->two_level ? PDN_PRECOND_TWOLEVEL
+                                     : (opts.precond == PDN_PRECOND_NONE ? PDN_PRECOND_NONE : PDN_PRECOND_JACOBI);
+        info->n_coarse = w->two_level ? w->nc : 0;
+        info->t_coarse_ms = w->coarse_ms;
     }
 }
 
@@ -1225,8 +1420,8 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
         launch();
         PDN_CUDA(cudaEventRecord(ev[2 * k + 1], st));
         if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
-            PDN_LAUNCH(ctx, cg_update_kernel, pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p, v3.p,
-                       v4.p, v5.p, aux.p);
+            PDN_LAUNCH(ctx, cg_update_kernel<false>, pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p,
+                       v3.p, v4.p, v5.p, aux.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
     }
     PDN_CUDA(cudaStreamSynchronize(st));
     double total = 0.0;

@@ -60,7 +60,7 @@ class SolverOptions:
     atol: float = 0.0
     max_iter: int = 0
     method: int = capi.METHOD_AUTO
-    precond: int = capi.PRECOND_JACOBI
+    precond: int = capi.PRECOND_AUTO
     device: int = 0
 
 

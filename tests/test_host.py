@@ -28,8 +28,8 @@ def test_strerror_and_struct_layout():
     assert lib.pdn_strerror(0) == b"ok"
     assert b"singular" in lib.pdn_strerror(capi.PDN_ESINGULAR)
     assert lib.pdn_strerror(capi.PDN_ENONMANIFOLD) == b"Non-manifold mesh"
-    assert ctypes.sizeof(capi.PdnOpts) == 40
-    assert ctypes.sizeof(capi.PdnInfo) == 72
+    assert ctypes.sizeof(capi.PdnOpts) == 48
+    assert ctypes.sizeof(capi.PdnInfo) == 88
 
 
 def test_no_gpu_means_loud_failure():
