@@ -261,48 +261,53 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 // apply
 // ------------------------------------------------------------------------------------------------
 // x_c = A_c^-1 r_c  (r_c arrives in fixed point, parity = iteration & 1); the other parity's
-// accumulator is cleared for the next restriction.  CTA b owns CO_RB consecutive rows at a time: every
-// thread issues the loads of its columns for ALL of them before the first use (the matrix is
-// L2-resident, the kernel is latency-bound), then one block reduction of CO_RB sums in a fixed order.
-constexpr int CO_RB = 8;
+// accumulator is cleared for the next restriction.  CTA b owns CO_RB consecutive rows: every thread
+// issues the loads of ALL its matrix entries before anything else (the matrix is L2-resident, the
+// kernel is latency-bound: 8.7 us with 8 rows per CTA and loads after the r_c conversion), then one
+// block reduction of CO_RB sums in a fixed order.
+constexpr int CO_RB = 4;
+constexpr int CO_JMAX = (CO_MAX + CO_BLK - 1) / CO_BLK;   // columns per thread
 __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const double *__restrict__ Ainv, const Scal *__restrict__ sc,
                                                               long long *__restrict__ rc_fix, double *__restrict__ xc) {
     __shared__ double rcd[CO_MAX];
     __shared__ double red[CO_RB][CO_BLK / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int row0 = blockIdx.x * CO_RB;
+    // the matrix entries do not depend on anything this iteration produced: request them first
+    double a[CO_RB][CO_JMAX];
+#pragma unroll
+    for (int q = 0; q < CO_RB; q++)
+#pragma unroll
+        for (int t = 0; t < CO_JMAX; t++) {
+            const int j = tid + t * CO_BLK;
+            a[q][t] = (row0 + q < nc && j < nc) ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.0;
+        }
     if (sc->done) return;
     const int par = sc->iter & 1;
     const long long *__restrict__ rc = rc_fix + (size_t)par * nc;
     long long *__restrict__ other = rc_fix + (size_t)(par ^ 1) * nc;
     const double scale = sqrt(fmax(sc->rr, 1e-300)) / CO_RFIX;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int j = tid; j < nc; j += CO_BLK) rcd[j] = (double)rc[j] * scale;
     __syncthreads();
-    for (int row0 = blockIdx.x * CO_RB; row0 < nc; row0 += gridDim.x * CO_RB) {
-        double acc[CO_RB];
+    double acc[CO_RB];
 #pragma unroll
-        for (int q = 0; q < CO_RB; q++) acc[q] = 0.0;
-        for (int j = tid; j < nc; j += CO_BLK) {
-            double a[CO_RB];
+    for (int q = 0; q < CO_RB; q++) {
+        acc[q] = 0.0;
 #pragma unroll
-            for (int q = 0; q < CO_RB; q++) a[q] = row0 + q < nc ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.0;
-            const double x = rcd[j];
-#pragma unroll
-            for (int q = 0; q < CO_RB; q++) acc[q] = fma(a[q], x, acc[q]);
+        for (int t = 0; t < CO_JMAX; t++) {
+            const int j = tid + t * CO_BLK;
+            if (j < nc) acc[q] = fma(a[q][t], rcd[j], acc[q]);
         }
 #pragma unroll
-        for (int q = 0; q < CO_RB; q++) {
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_down_sync(0xffffffffu, acc[q], o);
-            if (lane == 0) red[q][warp] = acc[q];
-        }
-        __syncthreads();
-        if (tid < CO_RB && row0 + tid < nc) {
-            double sum = 0.0;
-            for (int k = 0; k < CO_BLK / 32; k++) sum += red[tid][k];
-            xc[row0 + tid] = sum;
-            other[row0 + tid] = 0;
-        }
-        __syncthreads();
+        for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_down_sync(0xffffffffu, acc[q], o);
+        if (lane == 0) red[q][warp] = acc[q];
+    }
+    __syncthreads();
+    if (tid < CO_RB && row0 + tid < nc) {
+        double sum = 0.0;
+        for (int k = 0; k < CO_BLK / 32; k++) sum += red[tid][k];
+        xc[row0 + tid] = sum;
+        other[row0 + tid] = 0;
     }
 }
 

@@ -535,7 +535,7 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         // both parities are reduced (2 nc values): the idle one is all zeros
         pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
     }
-    const int cgrid = std::max(1, std::min(2 * ctx->n_sm, (w->nc + CO_RB - 1) / CO_RB));
+    const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
     PDN_LAUNCH(ctx, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_A.p, w->d_sc, w->rc_fix.p, w->xc.p);
     PDN_LAUNCH(ctx, coarse_z_kernel, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, w->r.p, w->agg.p,
                w->xc.p, w->z.p);

@@ -250,6 +250,46 @@ def test_solve_is_deterministic(ctx):
     assert np.array_equal(v1, v2) and i1.iterations == i2.iterations
 
 
+# ---- kernel (4'): two-level preconditioner -----------------------------------------------------
+@pytest.mark.parametrize("name,board,n_coarse", [
+    ("2layer_160", lambda: synth.board_2layer(160, n_via=5, size_mm=25.0, seed=21), 0),
+    ("2layer_160_c64", lambda: synth.board_2layer(160, n_via=5, size_mm=25.0, seed=21), 64),
+    ("8layer_60", lambda: synth.board_8layer(60, n_via=3, size_mm=40.0, seed=2), 300),
+    ("tht_standin_48", lambda: synth.board_via_tht_standin(48, seed=3), 0),       # internal nodes get aggregates
+])
+def test_two_level_preconditioner(ctx, name, board, n_coarse):
+    from padne_b200 import capi
+    fs = board().to_flat()
+    indptr, indices, data, rhs = gpu_assemble(ctx, fs)
+    vj, ij = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_JACOBI)
+    vt, it = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL, n_coarse=n_coarse)
+    assert ij.precond == "jacobi" and ij.n_coarse == 0
+    assert it.precond == "two-level" and it.n_coarse >= 4
+    assert it.iterations < ij.iterations                     # the coarse space pays
+    assert it.rel_residual <= RESIDUAL_RTOL
+    v_ref, _, _ = oracle.solve(indptr, indices, data, rhs)
+    assert voltage_error(vt, v_ref, fs.n_nodes) <= VOLTAGE_RTOL
+    assert voltage_error(vt, vj, fs.n_nodes) <= 1e-8
+    vt2, it2 = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL, n_coarse=n_coarse)
+    assert np.array_equal(vt, vt2) and it.iterations == it2.iterations   # fixed-point sums: bit-reproducible
+
+
+def test_two_level_needs_geometry_and_symmetry(ctx):
+    from padne_b200 import capi
+    fs, d = load_system(golden_system_files()[0])
+    ctx.set_csr(d["indptr"], d["indices"], d["data"])             # a foreign matrix carries no coordinates
+    with pytest.raises(NotImplementedError):
+        ctx.solve(d["r"], n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL)
+    v, info = ctx.solve(d["r"], n_nodes=fs.n_nodes)               # AUTO falls back to Jacobi
+    assert info.precond == "jacobi"
+    fs = synth.board_4layer_regulator(40, n_via=2, size_mm=12.0, seed=4).to_flat()
+    _, _, _, rhs = gpu_assemble(ctx, fs)
+    with pytest.raises(NotImplementedError):                      # regulator gains: BiCGSTAB keeps Jacobi
+        ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL)
+    v, info = ctx.solve(rhs, n_nodes=fs.n_nodes)
+    assert info.method == "bicgstab" and info.precond == "jacobi"
+
+
 @pytest.mark.parametrize("grid", [50, 180])       # 180: several work items per CTA (pipelined path)
 def test_spmv_matches_scipy(ctx, grid):
     fs = synth.board_8layer(grid, n_via=2, size_mm=30.0, seed=4).to_flat()
