@@ -20,7 +20,7 @@
 // Included by pdn_kernels.cuh (namespace pdnk).
 #pragma once
 
-constexpr int CO_MAX = 1776;          // largest coarse space: 12 rows x 1776 doubles per CTA = 170 KB
+constexpr int CO_MAX = PDN_CO_MAX;         // largest coarse space: 12 rows x 1776 doubles per CTA = 170 KB
 constexpr int CO_BLK = 256;
 constexpr double CO_RFIX = 1099511627776.0;   // 2^40: fixed-point steps per ||r|| in the restriction
 

@@ -45,14 +45,23 @@ template <typename T>
 struct DevBuf {
     T *p = nullptr;
     size_t cap = 0;  // elements
+    bool owned = true;   // false: p points into memory owned by somebody else (attach)
     DevBuf() = default;
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
     ~DevBuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
+        if (p && owned) cudaFree(p);
         p = nullptr;
         cap = 0;
+        owned = true;
+    }
+    // borrow n elements at ptr (never freed here)
+    void attach(T *ptr, size_t n) {
+        release();
+        p = ptr;
+        cap = n;
+        owned = false;
     }
     // contents are NOT preserved
     T *reserve(size_t n) {
@@ -67,6 +76,7 @@ struct DevBuf {
     void swap(DevBuf &o) {
         T *tp = p; p = o.p; o.p = tp;
         size_t tc = cap; cap = o.cap; o.cap = tc;
+        bool to = owned; owned = o.owned; o.owned = to;
     }
 };
 
@@ -185,6 +195,34 @@ void pdn_spmv_impl(pdn_ctx *ctx, const double *x, double *y, bool on_device);
 void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms);
 void pdn_solve_release(pdn_ctx *ctx);
 void pdn_assemble_release(pdn_ctx *ctx);
+
+// ---- peer-memory exchanges (pdn_peer.cuh / pdn_multi.cu) ---------------------------------------------
+constexpr int PDN_CO_MAX = 1776;          // largest coarse space (pdn_coarse.cuh)
+constexpr int PDN_PEER_MAX = 8;
+// arena layout, in 8-byte words
+constexpr size_t PDN_PA_HALO_FLAG = 0;                              // [PEER_MAX]
+constexpr size_t PDN_PA_RED_FLAG = 16;                              // [2][PEER_MAX]
+constexpr size_t PDN_PA_RC_FLAG = 32;                               // [2][PEER_MAX]
+constexpr size_t PDN_PA_RED_VAL = 64;                               // [2][PEER_MAX][4]
+constexpr size_t PDN_PA_RC_SLOT = 2 * PDN_CO_MAX;                   // both parities of the fixed-point r_c
+constexpr size_t PDN_PA_RC_VAL = 128;                               // [2][PEER_MAX][RC_SLOT]
+constexpr size_t PDN_PA_VEC = PDN_PA_RC_VAL + (size_t)2 * PDN_PEER_MAX * PDN_PA_RC_SLOT;   // [4][n_cap]
+constexpr int PDN_PA_NVEC = 4;            // halo-exchanged vectors living in the arena: z, ph, sh, x
+
+struct PdnPeerLink {
+    int world, me;
+    unsigned long long *arena[PDN_PEER_MAX];   // arena[k]: rank k's arena as mapped in this process
+    unsigned long long *epoch;                 // local: [0] halo, [1] dot sums, [2] coarse residual
+    int32_t *status;                           // local device status words
+};
+// true when the communicator exchanges through mapped peer memory (else NCCL collectives)
+bool pdn_peer_enabled(const pdn_ctx *ctx);
+// collective: (re)allocate the arena for vectors of n_cap doubles and map every peer's
+void pdn_peer_ensure(pdn_ctx *ctx, int64_t n_cap);
+PdnPeerLink pdn_peer_link(const pdn_ctx *ctx);
+double *pdn_peer_vec(const pdn_ctx *ctx, int which);   // vector `which` (0..3) inside the local arena
+size_t pdn_peer_vec_offset(const pdn_ctx *ctx, int which);   // its word offset inside every arena
+unsigned int *pdn_peer_ticket(const pdn_ctx *ctx);
 
 // multi-GPU plumbing (pdn_multi.cu); all collectives are enqueued on the context stream
 int pdn_comm_rank(const pdn_ctx *ctx);

@@ -297,4 +297,6 @@ __global__ void __launch_bounds__(RPB) sumsq_kernel(int64_t r0, int64_t n, const
     else *out = acc[0];
 }
 
+#include "pdn_peer.cuh"
+
 }  // namespace pdnk

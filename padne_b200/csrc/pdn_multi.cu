@@ -10,6 +10,7 @@
 // torch already loaded (2.28.x), otherwise the system library.  The few NCCL types used here are
 // re-declared so the build needs no NCCL headers and the library no link-time NCCL dependency.
 #include <dlfcn.h>
+#include <stdlib.h>
 
 #include "pdn_common.cuh"
 
@@ -20,6 +21,7 @@ typedef struct ncclComm *ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 constexpr int kNcclSuccess = 0;
 constexpr int kNcclSum = 0;
+constexpr int kNcclInt8 = 0;      // ncclInt8 / ncclChar
 constexpr int kNcclInt64 = 4;     // ncclInt64
 constexpr int kNcclFloat64 = 8;   // ncclFloat64
 
@@ -30,6 +32,7 @@ struct NcclApi {
     int (*CommDestroy)(ncclComm_t) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Broadcast)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
@@ -54,6 +57,7 @@ const NcclApi &nccl() {
     PDN_SYM(CommDestroy);
     PDN_SYM(AllReduce);
     PDN_SYM(Broadcast);
+    PDN_SYM(AllGather);
     PDN_SYM(Send);
     PDN_SYM(Recv);
     PDN_SYM(GroupStart);
@@ -76,13 +80,89 @@ const NcclApi &nccl() {
 struct PdnComm {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
+    // peer-memory exchanges (pdn_peer.cuh): one arena per rank, mapped into every peer through CUDA IPC
+    bool p2p = false;
+    unsigned long long *arena = nullptr;              // local
+    unsigned long long *peer[PDN_PEER_MAX] = {};      // peer[k] = rank k's arena mapped here (peer[rank] = arena)
+    int64_t n_cap = 0;                                // doubles per exchanged vector
+    unsigned long long *epoch = nullptr;              // device [4]
+    unsigned int *ticket = nullptr;                   // device [4]
 };
+
+static void peer_unmap(PdnComm *c) {
+    for (int k = 0; k < c->world && k < PDN_PEER_MAX; k++) {
+        if (k != c->rank && c->peer[k]) cudaIpcCloseMemHandle(c->peer[k]);
+        c->peer[k] = nullptr;
+    }
+    if (c->arena) cudaFree(c->arena);
+    c->arena = nullptr;
+    c->n_cap = 0;
+}
+
+bool pdn_peer_enabled(const pdn_ctx *ctx) { return ctx->comm && ctx->comm->p2p; }
+
+void pdn_peer_ensure(pdn_ctx *ctx, int64_t n) {
+    PdnComm *c = ctx->comm;
+    if (!c || !c->p2p || n <= c->n_cap) return;
+    cudaStream_t st = ctx->stream;
+    PDN_CUDA(cudaStreamSynchronize(st));
+    peer_unmap(c);
+    const int64_t n_cap = (n + n / 8 + 1024 + 31) / 32 * 32;
+    const size_t words = PDN_PA_VEC + (size_t)PDN_PA_NVEC * n_cap;
+    PDN_CUDA(cudaMalloc((void **)&c->arena, words * 8));
+    PDN_CUDA(cudaMemsetAsync(c->arena, 0, words * 8, st));
+    PDN_CUDA(cudaMemsetAsync(c->epoch, 0, 4 * sizeof(unsigned long long), st));   // the wait-cycle counters [4..7] keep counting
+    PDN_CUDA(cudaMemsetAsync(c->ticket, 0, 4 * sizeof(unsigned int), st));
+    // handles of all ranks (the all-gather also orders every rank's memset before any peer store)
+    cudaIpcMemHandle_t mine;
+    PDN_CUDA(cudaIpcGetMemHandle(&mine, c->arena));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DevBuf<char> hbuf;
+    hbuf.reserve((size_t)64 * c->world);
+    PDN_CUDA(cudaMemcpyAsync(hbuf.p + 64 * c->rank, &mine, 64, cudaMemcpyHostToDevice, st));
+    PDN_NCCL(nccl().AllGather(hbuf.p + 64 * c->rank, hbuf.p, 64, kNcclInt8, c->comm, st));
+    std::vector<cudaIpcMemHandle_t> all(c->world);
+    PDN_CUDA(cudaMemcpyAsync(all.data(), hbuf.p, (size_t)64 * c->world, cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    for (int k = 0; k < c->world; k++) {
+        if (k == c->rank) { c->peer[k] = c->arena; continue; }
+        void *ptr = nullptr;
+        PDN_CUDA(cudaIpcOpenMemHandle(&ptr, all[k], cudaIpcMemLazyEnablePeerAccess));
+        c->peer[k] = (unsigned long long *)ptr;
+    }
+    c->n_cap = n_cap;
+}
+
+PdnPeerLink pdn_peer_link(const pdn_ctx *ctx) {
+    PdnPeerLink L{};
+    const PdnComm *c = ctx->comm;
+    L.world = c->world;
+    L.me = c->rank;
+    for (int k = 0; k < c->world; k++) L.arena[k] = c->peer[k];
+    L.epoch = c->epoch;
+    L.status = ctx->d_status;
+    return L;
+}
+size_t pdn_peer_vec_offset(const pdn_ctx *ctx, int which) { return PDN_PA_VEC + (size_t)which * ctx->comm->n_cap; }
+double *pdn_peer_vec(const pdn_ctx *ctx, int which) {
+    return reinterpret_cast<double *>(ctx->comm->arena + pdn_peer_vec_offset(ctx, which));
+}
+unsigned int *pdn_peer_ticket(const pdn_ctx *ctx) { return ctx->comm->ticket; }
 
 int pdn_comm_rank(const pdn_ctx *ctx) { return ctx->comm ? ctx->comm->rank : 0; }
 int pdn_comm_world(const pdn_ctx *ctx) { return ctx->comm ? ctx->comm->world : 1; }
 
 void pdn_comm_release(pdn_ctx *ctx) {
     if (ctx->comm) {
+        if (ctx->comm->epoch && getenv("PADNE_B200_PEER_STATS")) {
+            unsigned long long h[8] = {};
+            cudaMemcpy(h, ctx->comm->epoch, sizeof h, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[padne_b200 rank %d] exchanges: halo %llu, dots %llu, coarse %llu; cycles waited: halo %llu, dots %llu, coarse %llu\n",
+                    ctx->comm->rank, h[0], h[1], h[2], h[4], h[5], h[6]);
+        }
+        peer_unmap(ctx->comm);
+        if (ctx->comm->epoch) cudaFree(ctx->comm->epoch);
+        if (ctx->comm->ticket) cudaFree(ctx->comm->ticket);
         if (ctx->comm->comm) nccl().CommDestroy(ctx->comm->comm);
         delete ctx->comm;
         ctx->comm = nullptr;
@@ -162,6 +242,14 @@ int pdn_comm_init(pdn_ctx *ctx, int rank, int world, const void *id128) {
         PDN_CUDA(cudaMemsetAsync(tmp.p, 0, 8 * sizeof(double), ctx->stream));
         pdn_comm_allreduce_sum(ctx, tmp.p, 4);
         PDN_CUDA(cudaStreamSynchronize(ctx->stream));
+        // peer-memory exchanges unless PADNE_B200_COMM=nccl (or more ranks than the arena has slots)
+        const char *mode = getenv("PADNE_B200_COMM");
+        c->p2p = world <= PDN_PEER_MAX && !(mode && strcmp(mode, "nccl") == 0);
+        if (c->p2p) {
+            PDN_CUDA(cudaMalloc((void **)&c->epoch, 8 * sizeof(unsigned long long)));
+            PDN_CUDA(cudaMemset(c->epoch, 0, 8 * sizeof(unsigned long long)));
+            PDN_CUDA(cudaMalloc((void **)&c->ticket, 4 * sizeof(unsigned int)));
+        }
     });
 }
 

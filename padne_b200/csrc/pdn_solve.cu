@@ -139,6 +139,7 @@ struct HaloPlan {
     int32_t n_send = 0, n_recv = 0;
     DevBuf<int32_t> send_idx, recv_idx;
     DevBuf<double> sendbuf, recvbuf;
+    HaloSend peer{};                            // the same plan for the peer-memory path (pdn_peer.cuh)
 };
 
 struct SolveWork {
@@ -260,16 +261,16 @@ static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, doub
 #endif
 }
 
+template <int WHICH>
+static void dist_reduce(pdn_ctx *ctx, SolveWork *w);
+
 // y = A x (+ fused dots) over the rows this rank owns.  Multi-GPU: the partial sums are all-reduced and
 // the scalar recurrence runs in scalar_kernel; x must already hold the halo entries.
 template <int MODE>
 static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
     if (is_dist(ctx)) {
         launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
-        if (MODE != PLAIN) {
-            pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
-            PDN_LAUNCH(ctx, scalar_kernel<MODE>, 1, 1, 0, w->d_sc, w->d_out);
-        }
+        if (MODE != PLAIN) dist_reduce<MODE>(ctx, w);
     } else {
         launch_sell_kernel<MODE, false>(ctx, w, x, y, aux);
     }
@@ -288,13 +289,37 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int32_t k, const int32
 static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
     if (!is_dist(ctx)) return;
     HaloPlan &h = w->halo;
+    if (h.n_send == 0 && h.n_recv == 0) return;
+    if (pdn_peer_enabled(ctx)) {
+        // the vector lives in the arena: owners store their interface entries into the peers' copies
+        int which = -1;
+        for (int v = 0; v < PDN_PA_NVEC; v++)
+            if (vec == pdn_peer_vec(ctx, v)) which = v;
+        if (which < 0) PDN_FAIL(PDN_ECUDA, "halo_exchange: vector is not inside the peer arena");
+        const PeerLink L = pdn_peer_link(ctx);
+        if (h.n_send > 0)
+            PDN_LAUNCH(ctx, halo_push_kernel, std::min(ctx->n_sm, pdn_blocks(h.n_send, 256)), 256, 0, L, h.peer,
+                       pdn_peer_vec_offset(ctx, which), h.send_idx.p, pdn_peer_ticket(ctx));
+        if (h.n_recv > 0) PDN_LAUNCH(ctx, halo_wait_kernel, 1, 32, 0, L, h.peer);
+        return;
+    }
     if (h.n_send > 0)
         PDN_LAUNCH(ctx, halo_pack_kernel, pdn_grid(ctx, h.n_send, 256, 4), 256, 0, h.n_send, h.send_idx.p, vec, h.sendbuf.p);
-    if (h.n_send > 0 || h.n_recv > 0)
-        pdn_comm_exchange(ctx, h.sendbuf.p, h.send_off.data(), h.send_cnt.data(), h.recvbuf.p, h.recv_off.data(),
-                          h.recv_cnt.data());
+    pdn_comm_exchange(ctx, h.sendbuf.p, h.send_off.data(), h.send_cnt.data(), h.recvbuf.p, h.recv_off.data(),
+                      h.recv_cnt.data());
     if (h.n_recv > 0)
         PDN_LAUNCH(ctx, halo_unpack_kernel, pdn_grid(ctx, h.n_recv, 256, 4), 256, 0, h.n_recv, h.recv_idx.p, h.recvbuf.p, vec);
+}
+
+// sum sc->part[0..2] over the ranks and run recurrence WHICH (scalar_kernel numbering)
+template <int WHICH>
+static void dist_reduce(pdn_ctx *ctx, SolveWork *w) {
+    if (pdn_peer_enabled(ctx)) {
+        PDN_LAUNCH(ctx, peer_reduce_kernel<WHICH>, 1, 32, 0, pdn_peer_link(ctx), w->d_sc, w->d_out);
+    } else {
+        pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
+        PDN_LAUNCH(ctx, scalar_kernel<WHICH>, 1, 1, 0, w->d_sc, w->d_out);
+    }
 }
 
 static void fetch_scal(pdn_ctx *ctx, SolveWork *w) {
@@ -533,7 +558,10 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w) {
 void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     if (is_dist(ctx)) {   // every rank restricted its own rows: exact integer sum, identical everywhere
         // both parities are reduced (2 nc values): the idle one is all zeros
-        pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
+        if (pdn_peer_enabled(ctx))
+            PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc);
+        else
+            pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
     }
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
     PDN_LAUNCH(ctx, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_A.p, w->d_sc, w->rc_fix.p, w->xc.p);
@@ -566,8 +594,7 @@ void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     if (dist) {
         PDN_LAUNCH(ctx, bicg_x_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p,
                    w->rhat.p, w->x.p, w->r.p, w->partials.p);
-        pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
-        PDN_LAUNCH(ctx, scalar_kernel<5>, 1, 1, 0, w->d_sc, w->d_out);
+        dist_reduce<5>(ctx, w);
     } else {
         PDN_LAUNCH(ctx, bicg_x_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p,
                    w->rhat.p, w->x.p, w->r.p, w->partials.p);
@@ -672,8 +699,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
             } else if (dist) {
                 PDN_LAUNCH(ctx, bicg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->rhat.p,
                            w->p.p, w->ph.p, w->partials.p);
-                pdn_comm_allreduce_sum(ctx, w->d_sc->part, 3);
-                PDN_LAUNCH(ctx, scalar_kernel<6>, 1, 1, 0, w->d_sc, w->d_out);
+                dist_reduce<6>(ctx, w);
             } else {
                 PDN_LAUNCH(ctx, bicg_init_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->rhat.p,
                            w->p.p, w->ph.p, w->partials.p);
@@ -857,6 +883,12 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     }
     h.n_send = (int32_t)send_idx.size();
     h.n_recv = (int32_t)recv_idx.size();
+    h.peer = HaloSend{};
+    for (int k = 0; k < world && k < PEER_MAX; k++) {
+        h.peer.off[k] = h.send_off[k];
+        h.peer.cnt[k] = h.send_cnt[k];
+        h.peer.recv_cnt[k] = h.recv_cnt[k];
+    }
     upload(ctx, h.send_idx, send_idx);
     upload(ctx, h.recv_idx, recv_idx);
     h.sendbuf.reserve((size_t)h.n_send + 1);
@@ -1293,7 +1325,18 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         }
     }
 
-    // vectors
+    // vectors.  The SpMV inputs (z, ph, sh, x) are the halo-exchanged ones: with peer-memory exchanges
+    // they live in the arena every peer has mapped
+    {
+        DevBuf<double> *ex[PDN_PA_NVEC] = {&w->z, &w->ph, &w->sh, &w->x};
+        if (pdn_peer_enabled(ctx)) {
+            pdn_peer_ensure(ctx, n);     // collective (same n on every rank)
+            for (int v = 0; v < PDN_PA_NVEC; v++) ex[v]->attach(pdn_peer_vec(ctx, v), (size_t)n);
+        } else {
+            for (int v = 0; v < PDN_PA_NVEC; v++)
+                if (!ex[v]->owned) ex[v]->release();
+        }
+    }
     w->x.reserve((size_t)n); w->r.reserve((size_t)n); w->z.reserve((size_t)n); w->p.reserve((size_t)n);
     w->s.reserve((size_t)n); w->w.reserve((size_t)n);
     if (method == PDN_METHOD_BICGSTAB) {
@@ -1304,6 +1347,15 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
 
     // ---- Krylov -------------------------------------------------------------------------------------
     KrylovResult kr = run_krylov(ctx, w, method, rtol, atol, max_iter, check_every);
+
+    if (is_dist(ctx)) {   // a peer that never answered (pdn_peer.cuh deadline)
+        int64_t detail = 0;
+        const int stt = pdn_status_fetch(ctx, &detail);
+        if (stt != 0) {
+            pdn_status_reset(ctx);
+            PDN_FAIL(stt, "solve: a peer rank did not answer within the deadline (%s)", pdn_strerror(stt));
+        }
+    }
 
     // ---- recovery: v = Z u + o, x = M^-1 C (r_n - L_nn v), full residual -------------------------------
     double *d_v = on_device ? v_out : w->full_b.p;
