@@ -297,6 +297,13 @@ def main():
     spmv_ms_warm = ctx.bench_spmv(reps=200, mode=0)
     spmv_ms_cold = ctx.bench_spmv(reps=50, mode=1)
     peak, peak_src = measured_peak_gbs()
+    traffic, traffic_src = None, None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
+        t = json.load(open(os.path.join(ROOT, "profiles", "spmv_traffic.json"))).get(args.config)
+        if t and world == 1 and args.n is None:
+            traffic, traffic_src = t["dram_bytes_read"] + t["dram_bytes_write"], t["source"]
+    except Exception:
+        pass
     achieved = alg_bytes / (spmv_ms * 1e-3) / 1e9
 
     if rank != 0:
@@ -319,16 +326,16 @@ def main():
                    "rel_residual": info.rel_residual, "residual_norm": info.residual_norm,
                    "t_krylov_ms": info.t_krylov_ms, "t_setup_ms": info.t_setup_ms,
                    "parallelism": ("single GPU" if world == 1 else
-                                   f"one board row-partitioned over {world} GPUs (NCCL halo exchange + dot all-reduce; "
-                                   f"assembly replicated)" if partitioned else f"{world} independent boards, one per GPU"),
+                                   f"one board row-partitioned over {world} GPUs (halo, dot and coarse-residual exchanges as "
+                                   f"peer-memory stores over NVLink, NCCL for setup; assembly replicated)" if partitioned else f"{world} independent boards, one per GPU"),
                    "l2": "256 MiB written between timed steps; per-step working set exceeds the 126 MB L2"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": t_e2e_ms / args.steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "pdnk::sell_spmv_kernel<CG> (SELL-32-sigma SpMV + fused r.z, z.w, r.r)",
+        "roofline": {"bound": "hbm", "kernel": "pdnk::sell_tma_kernel<CG> (SELL-32-sigma SpMV, per-warp TMA ring, fused r.z, z.w, r.r)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                      "ms_per_launch_in_situ": spmv_ms, "ms_per_launch_warm_l2": spmv_ms_warm,
                      "ms_per_launch_cold_l2": spmv_ms_cold,
                      "note": "matrix + vectors of this config are close to the L2 size; in-situ timing "
