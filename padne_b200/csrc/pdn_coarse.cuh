@@ -157,100 +157,126 @@ __global__ void __launch_bounds__(CO_BLK) coarse_accum_special_kernel(SellOp A, 
     }
 }
 
-// fixed point -> double, symmetrised
+// fixed point -> double (symm: averaged with the transpose -- a no-op for a symmetric operator)
 __global__ void __launch_bounds__(CO_BLK) coarse_convert_kernel(int32_t nc, double inv_fix, const long long *__restrict__ acc,
-                                                                double *__restrict__ Ac) {
+                                                                double *__restrict__ Ac, int symm) {
     const int64_t tot = (int64_t)nc * nc;
     for (int64_t e = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; e < tot; e += (int64_t)gridDim.x * CO_BLK) {
         const int32_t i = (int32_t)(e / nc), j = (int32_t)(e - (int64_t)i * nc);
-        Ac[e] = 0.5 * ((double)acc[e] + (double)acc[(int64_t)j * nc + i]) * inv_fix;
+        Ac[e] = symm ? 0.5 * ((double)acc[e] + (double)acc[(int64_t)j * nc + i]) * inv_fix : (double)acc[e] * inv_fix;
     }
 }
 
 // ------------------------------------------------------------------------------------------------
 // in-place inverse of the SPD coarse matrix: cooperative blocked Gauss-Jordan (no pivoting).
 // CTA b owns rows [b*R, (b+1)*R) and keeps them in shared memory.  Block step b (the sweep operator over
-// the pivot block K = rows of CTA b): the owner sweeps its own rows (R local steps), publishes them,
-// one grid barrier, every other CTA applies  A_i,j <- (j in K ? 0 : A_i,j) - sum_q A_i,K[q] * piv_q,j.
+// the pivot block K = rows of CTA b, D = A_KK):
+//   owner:   A_K,j <- D^-1 A_K,j (j not in K),  A_KK <- D^-1; D^-1 is an R x R Gauss-Jordan by the whole
+//            CTA, the product is one pass over the rows; the new rows are published to piv[b] and
+//            flag[b] is released.  (v1 swept the R pivots one after the other over all nc columns: 2.4 us
+//            per pivot, 2.3 ms at nc = 968, and taller blocks made it slower.)
+//   others:  wait for flag[b] only -- no grid-wide barrier, piv[b] is never reused -- then
+//            A_i,j <- (j in K ? 0 : A_i,j) - sum_q A_i,K[q] * piv_q,j.
 // Launched cooperatively (all CTAs co-resident); status[0] != 0 on a non-positive pivot / timeout.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool grid_barrier(unsigned int *counter, unsigned int target, int32_t *status) {
-    __syncthreads();
+__device__ __forceinline__ bool flag_wait(const unsigned int *flag, int32_t *status) {
     __shared__ int ok;
+    __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1u);
         const long long t0 = clock64();
         int good = 1;
         while (true) {
             unsigned int v;
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter));
-            if (v >= target) break;
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+            if (v != 0u) break;
             if (clock64() - t0 > 4000000000LL) { good = 0; atomicExch(&status[0], PDN_ECUDA); break; }   // ~2 s
         }
         ok = good;
-        __threadfence();
     }
     __syncthreads();
     return ok != 0;
 }
 
+// out_i,j = sum_q c[i][q] * P_q,j for four columns per thread at a time: the 16 x 4 operand block sits
+// in registers, every multiplier is read from shared memory once per four columns (one LDS per FMA made
+// both phases LDS-bound: 22 us per block step).
+//   OWNER:  P = my old rows, A_i,j <- out (j not in K) | c[i][j-k0] (j in K), also stored to pb
+//   else:   P = pb (published pivot rows),  A_i,j <- (j in K ? 0 : A_i,j) - out
+template <bool OWNER>
+__device__ __forceinline__ void co_rank_update(double *rows, const double (*cs)[16], double *pb, int nc, int ni, int nk,
+                                               int k0) {
+    const int tid = threadIdx.x;
+    for (int j0 = tid; j0 < nc; j0 += 4 * CO_BLK) {
+        double p[4][16];
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            const int j = j0 + t * CO_BLK;
+#pragma unroll
+            for (int q = 0; q < 16; q++)
+                p[t][q] = (j < nc && q < nk) ? (OWNER ? rows[q * nc + j] : __ldcg(&pb[q * nc + j])) : 0.0;
+        }
+        for (int i = 0; i < ni; i++) {
+            double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+            for (int q = 0; q < 16; q += 2) {
+                const double2 c = *reinterpret_cast<const double2 *>(&cs[i][q]);
+#pragma unroll
+                for (int t = 0; t < 4; t++) acc[t] += c.x * p[t][q] + c.y * p[t][q + 1];
+            }
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int j = j0 + t * CO_BLK;
+                if (j >= nc) continue;
+                const bool in_k = j >= k0 && j < k0 + nk;
+                if (OWNER) {
+                    const double o = in_k ? cs[i][j - k0] : acc[t];
+                    rows[i * nc + j] = o;
+                    pb[i * nc + j] = o;
+                } else {
+                    rows[i * nc + j] = (in_k ? 0.0 : rows[i * nc + j]) - acc[t];
+                }
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, int32_t R, double *__restrict__ A,
-                                                                  double *__restrict__ piv /*[2][R * nc]*/,
-                                                                  unsigned int *counter, int32_t *status) {
+                                                                  double *__restrict__ piv /*[n_blk][R * nc]*/,
+                                                                  unsigned int *flags /*[n_blk], zeroed*/, int32_t *status) {
     extern __shared__ double rows[];                 // [R][nc]
-    __shared__ double cs[16][16];                    // multipliers (R <= 16)
+    __shared__ __align__(16) double cs[16][16];      // D, then D^-1 (owner) / multipliers (others); R <= 16
     const int b = blockIdx.x, tid = threadIdx.x;
     const int r0 = b * R;
     const int nr = r0 >= nc ? 0 : (r0 + R <= nc ? R : nc - r0);
     for (int e = tid; e < nr * nc; e += CO_BLK) rows[e] = A[(size_t)r0 * nc + e];
     __syncthreads();
     const int n_blk = (nc + R - 1) / R;
-    unsigned int target = 0;
+    const int di = tid >> 4, dj = tid & 15;          // CO_BLK == 256: one thread per entry of cs
     for (int kb = 0; kb < n_blk; kb++) {
         const int k0 = kb * R, nk = k0 + R <= nc ? R : nc - k0;
-        double *pb = piv + (size_t)(kb & 1) * R * nc;      // double-buffered: one barrier per block step
+        double *pb = piv + (size_t)kb * R * nc;
         if (kb == b) {
-            // sweep my own rows over the pivots k0 .. k0+nk-1
+            // D^-1 in place (identity padding beyond nk)
+            cs[di][dj] = (di < nk && dj < nk) ? rows[di * nc + k0 + dj] : (di == dj ? 1.0 : 0.0);
             for (int q = 0; q < nk; q++) {
-                const int k = k0 + q;
-                if (tid < nk) cs[0][tid] = rows[tid * nc + k];
                 __syncthreads();
-                const double p = cs[0][q];
+                const double p = cs[q][q], rq = cs[q][dj], cq = cs[di][q], cur = cs[di][dj];
+                __syncthreads();
                 if (!(p > 0.0) && tid == 0) atomicExch(&status[0], PDN_ESINGULAR);
                 const double ip = 1.0 / p;
-                for (int j = tid; j < nc; j += CO_BLK) {
-                    const double pr = (j == k ? 1.0 : rows[q * nc + j]) * ip;
-                    rows[q * nc + j] = pr;
-                    for (int i = 0; i < nk; i++) {
-                        if (i == q) continue;
-                        const double cur = j == k ? 0.0 : rows[i * nc + j];
-                        rows[i * nc + j] = cur - cs[0][i] * pr;
-                    }
-                }
-                __syncthreads();
+                const double pr = (dj == q ? 1.0 : rq) * ip;
+                cs[di][dj] = di == q ? pr : (dj == q ? 0.0 : cur) - cq * pr;
             }
-            for (int e = tid; e < nk * nc; e += CO_BLK) pb[e] = rows[e];
-        }
-        target += gridDim.x;
-        if (!grid_barrier(counter, target, status)) return;
-        if (kb != b && nr > 0) {
-            // A_i,j <- (j in K ? 0 : A_i,j) - sum_q A_i,K[q] (old) * piv_q,j
-            for (int e = tid; e < nr * nk; e += CO_BLK) cs[e / nk][e % nk] = rows[(e / nk) * nc + k0 + (e % nk)];
             __syncthreads();
-            for (int j = tid; j < nc; j += CO_BLK) {
-                double pj[16];
-#pragma unroll
-                for (int q = 0; q < 16; q++) pj[q] = q < nk ? __ldcg(&pb[q * nc + j]) : 0.0;
-                const bool in_k = j >= k0 && j < k0 + nk;
-                for (int i = 0; i < nr; i++) {
-                    double sacc = in_k ? 0.0 : rows[i * nc + j];
-#pragma unroll
-                    for (int q = 0; q < 16; q++)
-                        if (q < nk) sacc -= cs[i][q] * pj[q];
-                    rows[i * nc + j] = sacc;
-                }
-            }
+            co_rank_update<true>(rows, cs, pb, nc, nk, nk, k0);
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + kb), "r"(1u) : "memory");
+        } else {
+            if (!flag_wait(flags + kb, status)) return;
+            cs[di][dj] = (di < nr && dj < nk) ? rows[di * nc + k0 + dj] : 0.0;
+            __syncthreads();
+            co_rank_update<false>(rows, cs, pb, nc, nr, nk, k0);
             __syncthreads();
         }
     }
@@ -260,7 +286,8 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 // ------------------------------------------------------------------------------------------------
 // apply
 // ------------------------------------------------------------------------------------------------
-// x_c = A_c^-1 r_c  (r_c arrives in fixed point, parity = iteration & 1); the other parity's
+// x_c = A_c^-1 r_c  (r_c arrives in fixed point, in slot `slot`, or iteration & 1 if slot < 0, scaled by
+// 2^40 / (boost ||r||)); the other slot's
 // accumulator is cleared for the next restriction.  CTA b owns CO_RB consecutive rows: every thread
 // issues the loads of ALL its matrix entries before anything else (the matrix is L2-resident, the
 // kernel is latency-bound: 8.7 us with 8 rows per CTA and loads after the r_c conversion), then one
@@ -268,7 +295,8 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 constexpr int CO_RB = 4;
 constexpr int CO_JMAX = (CO_MAX + CO_BLK - 1) / CO_BLK;   // columns per thread
 __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const double *__restrict__ Ainv, const Scal *__restrict__ sc,
-                                                              long long *__restrict__ rc_fix, double *__restrict__ xc) {
+                                                              long long *__restrict__ rc_fix, double *__restrict__ xc,
+                                                              int slot, double boost) {
     __shared__ double rcd[CO_MAX];
     __shared__ double red[CO_RB][CO_BLK / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -283,10 +311,10 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const 
             a[q][t] = (row0 + q < nc && j < nc) ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.0;
         }
     if (sc->done) return;
-    const int par = sc->iter & 1;
+    const int par = slot < 0 ? (sc->iter & 1) : slot;
     const long long *__restrict__ rc = rc_fix + (size_t)par * nc;
     long long *__restrict__ other = rc_fix + (size_t)(par ^ 1) * nc;
-    const double scale = sqrt(fmax(sc->rr, 1e-300)) / CO_RFIX;
+    const double scale = boost * sqrt(fmax(sc->rr, 1e-300)) / CO_RFIX;
     for (int j = tid; j < nc; j += CO_BLK) rcd[j] = (double)rc[j] * scale;
     __syncthreads();
     double acc[CO_RB];

@@ -206,17 +206,31 @@ __global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, con
     }
 }
 
-// BiCGSTAB step 2:  s = r - alpha v;  sh = dinv s
+// the vectors BiCGSTAB restricts (s, p) are not bounded by ||r||: the fixed-point scale leaves 2^10 more
+// headroom than in PCG (resolution 2^-30 ||r|| per entry)
+constexpr double BICG_BOOST = 1024.0;
+
+// BiCGSTAB step 2:  s = r - alpha v;  sh = dinv s   (TL: sh comes from coarse_z_kernel, s is restricted)
+template <bool TL>
 __global__ void __launch_bounds__(RPB) bicg_s_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                      const double *__restrict__ dinv,
                                                      const double *__restrict__ r, const double *__restrict__ v,
-                                                     double *__restrict__ s, double *__restrict__ sh) {
+                                                     double *__restrict__ s, double *__restrict__ sh,
+                                                     const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
     if (sc->done) return;
     const double alpha = sc->alpha;
-    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
-        const double si = r[i] - alpha * v[i];
-        s[i] = si;
-        sh[i] = dinv[i] * si;
+    const double fix = TL ? CO_RFIX / (BICG_BOOST * sqrt(fmax(sc->rr, 1e-300))) : 0.0;
+    unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix);   // slot 0
+    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool act = i < n;
+        double si = 0.0;
+        if (act) {
+            si = r[i] - alpha * v[i];
+            s[i] = si;
+            if (!TL) sh[i] = dinv[i] * si;
+        }
+        if (TL) restrict_add(si, act ? agg[i] : -1, fix, rc);
     }
 }
 
@@ -244,34 +258,54 @@ __global__ void __launch_bounds__(RPB) bicg_x_kernel(int64_t r0, int64_t n, Scal
     else bicg_x_finalize(acc, sc);
 }
 
-// BiCGSTAB step 5:  p = r + beta (p - omega v);  ph = dinv p
+// BiCGSTAB step 5:  p = r + beta (p - omega v);  ph = dinv p   (TL: p is restricted into slot 1)
+template <bool TL>
 __global__ void __launch_bounds__(RPB) bicg_p_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                      const double *__restrict__ dinv,
                                                      const double *__restrict__ r, const double *__restrict__ v,
-                                                     double *__restrict__ p, double *__restrict__ ph) {
+                                                     double *__restrict__ p, double *__restrict__ ph,
+                                                     const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
     if (sc->done) return;
     const double beta = sc->beta, omega = sc->omega;
-    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
-        const double pi = r[i] + beta * (p[i] - omega * v[i]);
-        p[i] = pi;
-        ph[i] = dinv[i] * pi;
+    const double fix = TL ? CO_RFIX / (BICG_BOOST * sqrt(fmax(sc->rr, 1e-300))) : 0.0;
+    unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (TL ? nc : 0);   // slot 1
+    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool act = i < n;
+        double pi = 0.0;
+        if (act) {
+            pi = r[i] + beta * (p[i] - omega * v[i]);
+            p[i] = pi;
+            if (!TL) ph[i] = dinv[i] * pi;
+        }
+        if (TL) restrict_add(pi, act ? agg[i] : -1, fix, rc);
     }
 }
 
 // BiCGSTAB start from residual r:  rhat = r; p = r; ph = dinv p; rho = r.r; rr = r.r
-template <bool DIST>
+// (TL: p is restricted into slot 1 with the scale of the CURRENT sc->rr, which the host set to ||r||^2)
+template <bool DIST, bool TL>
 __global__ void __launch_bounds__(RPB) bicg_init_kernel(int64_t r0, int64_t n, Scal *sc, const double *__restrict__ dinv,
                                                         const double *__restrict__ r, double *__restrict__ rhat,
                                                         double *__restrict__ p, double *__restrict__ ph,
-                                                        double *partials) {
+                                                        double *partials, const int32_t *__restrict__ agg,
+                                                        long long *rc_fix, int32_t nc) {
     __shared__ double red[3][RPB / 32];
     double acc[3] = {0.0, 0.0, 0.0};
-    for (int64_t i = r0 + (int64_t)blockIdx.x * RPB + threadIdx.x; i < n; i += (int64_t)gridDim.x * RPB) {
-        const double ri = r[i];
-        rhat[i] = ri;
-        p[i] = ri;
-        ph[i] = dinv[i] * ri;
-        acc[0] += ri * ri;
+    const double fix = TL ? CO_RFIX / (BICG_BOOST * sqrt(fmax(sc->rr, 1e-300))) : 0.0;
+    unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (TL ? nc : 0);   // slot 1
+    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool act = i < n;
+        double ri = 0.0;
+        if (act) {
+            ri = r[i];
+            rhat[i] = ri;
+            p[i] = ri;
+            if (!TL) ph[i] = dinv[i] * ri;
+            acc[0] += ri * ri;
+        }
+        if (TL) restrict_add(ri, act ? agg[i] : -1, fix, rc);
     }
     if (!grid_reduce<3>(acc, partials, &sc->ticket[1], red)) return;
     if (threadIdx.x != 0) return;

@@ -119,11 +119,12 @@ __global__ void peer_reduce_kernel(PeerLink L, Scal *sc, double *out) {
 }
 
 // ---- coarse residual -----------------------------------------------------------------------------------
-// the active parity of rc_fix (this rank's fixed-point partial sums, nc values) -> exact sum over the
-// ranks, in place
-__global__ void __launch_bounds__(256) peer_sum_i64_kernel(PeerLink L, const Scal *__restrict__ sc, long long *rc_fix, int32_t nc) {
+// the active slot of rc_fix (this rank's fixed-point partial sums, nc values; slot < 0: iteration parity)
+// -> exact sum over the ranks, in place
+__global__ void __launch_bounds__(256) peer_sum_i64_kernel(PeerLink L, const Scal *__restrict__ sc, long long *rc_fix, int32_t nc,
+                                                           int rc_slot) {
     if (sc->done) return;    // identical on every rank
-    long long *rc = rc_fix + (size_t)(sc->iter & 1) * nc;
+    long long *rc = rc_fix + (size_t)(rc_slot < 0 ? (sc->iter & 1) : rc_slot) * nc;
     const int32_t cnt = nc;
     const unsigned long long e = L.epoch[2] + 1;
     const size_t slot = (size_t)(e & 1) * PEER_MAX;

@@ -274,7 +274,7 @@ def test_two_level_preconditioner(ctx, name, board, n_coarse):
     assert np.array_equal(vt, vt2) and it.iterations == it2.iterations   # fixed-point sums: bit-reproducible
 
 
-def test_two_level_needs_geometry_and_symmetry(ctx):
+def test_two_level_needs_geometry(ctx):
     from padne_b200 import capi
     fs, d = load_system(golden_system_files()[0])
     ctx.set_csr(d["indptr"], d["indices"], d["data"])             # a foreign matrix carries no coordinates
@@ -282,12 +282,27 @@ def test_two_level_needs_geometry_and_symmetry(ctx):
         ctx.solve(d["r"], n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL)
     v, info = ctx.solve(d["r"], n_nodes=fs.n_nodes)               # AUTO falls back to Jacobi
     assert info.precond == "jacobi"
-    fs = synth.board_4layer_regulator(40, n_via=2, size_mm=12.0, seed=4).to_flat()
-    _, _, _, rhs = gpu_assemble(ctx, fs)
-    with pytest.raises(NotImplementedError):                      # regulator gains: BiCGSTAB keeps Jacobi
-        ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL)
-    v, info = ctx.solve(rhs, n_nodes=fs.n_nodes)
-    assert info.method == "bicgstab" and info.precond == "jacobi"
+
+
+@pytest.mark.parametrize("grid,n_coarse", [(40, 0), (120, 200)])
+def test_two_level_bicgstab_regulator(ctx, grid, n_coarse):
+    # regulator gains make the reduced operator non-symmetric: BiCGSTAB, preconditioned twice per
+    # iteration through the same (non-symmetrised) coarse inverse
+    from padne_b200 import capi
+    fs = synth.board_4layer_regulator(grid, n_via=2, size_mm=12.0, seed=4).to_flat()
+    indptr, indices, data, rhs = gpu_assemble(ctx, fs)
+    vj, ij = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_JACOBI)
+    vt, it = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL, n_coarse=n_coarse)
+    assert ij.method == "bicgstab" and it.method == "bicgstab"
+    assert it.precond == "two-level" and it.n_coarse >= 4
+    assert it.iterations < ij.iterations
+    assert it.rel_residual <= RESIDUAL_RTOL
+    v_ref, _, _ = oracle.solve(indptr, indices, data, rhs)
+    assert voltage_error(vt, v_ref, fs.n_nodes) <= VOLTAGE_RTOL
+    vt2, it2 = ctx.solve(rhs, n_nodes=fs.n_nodes, precond=capi.PRECOND_TWOLEVEL, n_coarse=n_coarse)
+    assert np.array_equal(vt, vt2) and it.iterations == it2.iterations
+    va, ia = ctx.solve(rhs, n_nodes=fs.n_nodes)                   # AUTO picks it for n >= 1024
+    assert ia.precond == "two-level"
 
 
 @pytest.mark.parametrize("grid", [50, 180])       # 180: several work items per CTA (pipelined path)
