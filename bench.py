@@ -305,6 +305,8 @@ def main():
     except Exception:
         pass
     achieved = alg_bytes / (spmv_ms * 1e-3) / 1e9
+    if world > 1 and os.environ.get("PADNE_B200_PEER_STATS"):
+        ctx.comm_destroy()                  # prints the per-exchange wait cycles (collective: every rank)
 
     if rank != 0:
         if world > 1:

@@ -23,6 +23,15 @@
 constexpr int CO_MAX = PDN_CO_MAX;         // largest coarse space: 12 rows x 1776 doubles per CTA = 170 KB
 constexpr int CO_BLK = 256;
 constexpr double CO_RFIX = 1099511627776.0;   // 2^40: fixed-point steps per ||r|| in the restriction
+// PCG restricts with 32-bit fixed point (one redux.sync instead of three, a fraction of the integer work:
+// cg_update_kernel<TL> was instruction-issue bound, ~250 instructions per 32 rows).  2^22 steps per ||r_k||,
+// entries clamped to +-(2^26 - 1) so that 32 lanes cannot overflow: 16x headroom for a residual that grows in
+// one step.  The quantisation (2.4e-7 ||r|| per entry) only perturbs the preconditioner.
+#ifndef PDN_RESTRICT_WIDE
+#define PDN_RESTRICT_WIDE 0
+#endif
+constexpr double CO_RFIX32 = PDN_RESTRICT_WIDE ? CO_RFIX : 4194304.0;
+constexpr double CO_BOOST32 = CO_RFIX / CO_RFIX32;   // what coarse_apply_kernel multiplies back
 
 struct CoarseGeom {
     int n_mesh;
@@ -354,6 +363,14 @@ __global__ void __launch_bounds__(CO_BLK) coarse_z_kernel(int64_t r0, int64_t n,
 // restriction of one residual entry into the fixed-point accumulator (called by the update kernels,
 // whole warps converged).  Lanes with the same aggregate are summed with three redux.sync over 19-bit
 // limbs of the biased value (|value| < 2^56), one integer atomic per distinct aggregate in the warp.
+__device__ __forceinline__ void restrict_add_narrow(double ri, int32_t a, double fix, unsigned long long *rc) {
+    int q = __double2int_rn(ri * fix);             // saturating
+    q = max(min(q, 67108863), -67108863);
+    const unsigned peers = __match_any_sync(0xffffffffu, a);
+    const int sum = __reduce_add_sync(peers, q);
+    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && a >= 0 && sum != 0)
+        atomicAdd(&rc[a], (unsigned long long)(long long)sum);
+}
 __device__ __forceinline__ void restrict_add(double ri, int32_t a, double fix, unsigned long long *rc) {
     const double lim = 72057594037927935.0;   // 2^56 - 1
     double q = ri * fix;

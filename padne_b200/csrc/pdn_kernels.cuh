@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, c
                                                         const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
     if (sc->done) return;
     const double alpha = sc->alpha, beta = sc->beta;
-    const double fix = TL ? CO_RFIX / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
+    const double fix = TL ? CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
     unsigned long long *rc = TL ? reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc : nullptr;
     for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
         const int64_t i = i0 + threadIdx.x;
@@ -179,7 +179,10 @@ __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, c
             r[i] = ri;
             if (!TL) z[i] = dinv[i] * ri;
         }
-        if (TL) restrict_add(ri, act ? agg[i] : -1, fix, rc);
+        if (TL) {
+            if (PDN_RESTRICT_WIDE) restrict_add(ri, act ? agg[i] : -1, fix, rc);
+            else restrict_add_narrow(ri, act ? agg[i] : -1, fix, rc);
+        }
     }
 }
 
@@ -190,7 +193,7 @@ __global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, con
                                                       const double *__restrict__ r, double *__restrict__ z,
                                                       double *__restrict__ p, double *__restrict__ s,
                                                       const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
-    const double fix = TL ? CO_RFIX / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
+    const double fix = TL ? CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
     unsigned long long *rc = TL ? reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc : nullptr;
     for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
         const int64_t i = i0 + threadIdx.x;
@@ -202,7 +205,10 @@ __global__ void __launch_bounds__(RPB) cg_init_kernel(int64_t r0, int64_t n, con
             p[i] = 0.0;
             s[i] = 0.0;
         }
-        if (TL) restrict_add(ri, act ? agg[i] : -1, fix, rc);
+        if (TL) {
+            if (PDN_RESTRICT_WIDE) restrict_add(ri, act ? agg[i] : -1, fix, rc);
+            else restrict_add_narrow(ri, act ? agg[i] : -1, fix, rc);
+        }
     }
 }
 

@@ -205,6 +205,9 @@ __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(Sell
 #ifndef PDN_SELL_TW
 #define PDN_SELL_TW 12
 #endif
+#ifndef PDN_SELL_EVICT
+#define PDN_SELL_EVICT 1
+#endif
 #ifndef PDN_SELL_TMINB
 #define PDN_SELL_TMINB 2
 #endif
@@ -226,6 +229,9 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         if (sc->done) return;
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#if PDN_SELL_EVICT
+    const uint64_t l2pol = tma::policy_evict_first();
+#endif
     unsigned char *ring = st_smem + (size_t)warp * ST_NSLOT * ST_SLOT_BYTES;
     uint64_t *bars = reinterpret_cast<uint64_t *>(st_smem + (size_t)ST_WARPS * ST_NSLOT * ST_SLOT_BYTES) + warp * ST_NSLOT;
     double(*red)[ST_WARPS] = reinterpret_cast<double(*)[ST_WARPS]>(
@@ -266,8 +272,13 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
             const int q = (int)(j % ST_NSLOT);
             unsigned char *slot = ring + (size_t)q * ST_SLOT_BYTES;
             tma::mbar_expect_tx(&bars[q], (uint32_t)cnt * 12u);
+#if PDN_SELL_EVICT
+            tma::bulk_g2s_hint(slot, A.va + o0, (uint32_t)cnt * 8u, &bars[q], l2pol);
+            tma::bulk_g2s_hint(slot + (size_t)ST_SLOT_ENT * 8, A.ci + o0, (uint32_t)cnt * 4u, &bars[q], l2pol);
+#else
             tma::bulk_g2s(slot, A.va + o0, (uint32_t)cnt * 8u, &bars[q]);
             tma::bulk_g2s(slot + (size_t)ST_SLOT_ENT * 8, A.ci + o0, (uint32_t)cnt * 4u, &bars[q]);
+#endif
         }
     };
 

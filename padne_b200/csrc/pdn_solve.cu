@@ -28,6 +28,8 @@
 // FULL system is reported exactly as solver.py:775.
 #include <math.h>
 
+#include <chrono>
+#include <string>
 #include <algorithm>
 #include <map>
 #include <unordered_map>
@@ -286,8 +288,16 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int32_t k, const int32
     for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) vec[idx[i]] = buf[i];
 }
 
+// PADNE_B200_DIST_SKIP=halo,dots,rc leaves an exchange out of the iteration (profiles/dist_probe.py: what does
+// each one cost?).  The numbers a solve returns with it are garbage by construction.
+static bool dist_skip(const char *what) {
+    const char *e = getenv("PADNE_B200_DIST_SKIP");
+    return e && strstr(e, what) != nullptr;
+}
+
 static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
     if (!is_dist(ctx)) return;
+    if (dist_skip("halo")) return;
     HaloPlan &h = w->halo;
     if (h.n_send == 0 && h.n_recv == 0) return;
     if (pdn_peer_enabled(ctx)) {
@@ -314,6 +324,10 @@ static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
 // sum sc->part[0..2] over the ranks and run recurrence WHICH (scalar_kernel numbering)
 template <int WHICH>
 static void dist_reduce(pdn_ctx *ctx, SolveWork *w) {
+    if (dist_skip("dots")) {
+        PDN_LAUNCH(ctx, scalar_kernel<WHICH>, 1, 1, 0, w->d_sc, w->d_out);
+        return;
+    }
     if (pdn_peer_enabled(ctx)) {
         PDN_LAUNCH(ctx, peer_reduce_kernel<WHICH>, 1, 32, 0, pdn_peer_link(ctx), w->d_sc, w->d_out);
     } else {
@@ -559,7 +573,7 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w) {
 // was restricted and the preconditioned one
 void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, double boost, const double *src,
                                double *dst) {
-    if (is_dist(ctx)) {   // every rank restricted its own rows: exact integer sum, identical everywhere
+    if (is_dist(ctx) && !dist_skip("rc")) {   // every rank restricted its own rows: exact integer sum, identical everywhere
         if (pdn_peer_enabled(ctx))
             PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, slot);
         else   // both slots are reduced (2 nc values): the idle one is all zeros
@@ -578,7 +592,7 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     if (w->two_level) {
         PDN_LAUNCH(ctx, cg_update_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                    w->x.p, w->r.p, w->agg.p, w->rc_fix.p, w->nc);
-        enqueue_coarse_correction(ctx, w, vgrid, -1, 1.0, w->r.p, w->z.p);
+        enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p);
     } else {
         PDN_LAUNCH(ctx, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                    w->x.p, w->r.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
@@ -710,7 +724,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
                 PDN_LAUNCH(ctx, cg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
                            w->s.p, w->agg.p, w->rc_fix.p, w->nc);
-                enqueue_coarse_correction(ctx, w, vgrid, -1, 1.0, w->r.p, w->z.p);
+                enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p);
             } else if (method == PDN_METHOD_PCG) {
                 PDN_LAUNCH(ctx, cg_init_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
                            w->s.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
@@ -843,16 +857,45 @@ __global__ void __launch_bounds__(256) halo_mark_kernel(SellOp A, int64_t n_slic
     }
 }
 
-// append (column, mask) of every marked column; with cap == 0 it only counts
-__global__ void __launch_bounds__(256) halo_collect_kernel(int64_t n, const uint32_t *__restrict__ needmask, int32_t cap,
-                                                           int32_t *count, int32_t *__restrict__ o_col,
-                                                           int32_t *__restrict__ o_mask) {
-    for (int64_t c = (int64_t)blockIdx.x * 256 + threadIdx.x; c < n; c += (int64_t)gridDim.x * 256) {
-        const uint32_t m = needmask[c];
-        if (!m) continue;
-        const int32_t slot = atomicAdd(count, 1);
-        if (slot < cap) { o_col[slot] = (int32_t)c; o_mask[slot] = (int32_t)m; }
+// The send / receive lists are ordered compactions of needmask (flag -> exclusive scan -> scatter), built on
+// the device: a board with many vias has ~1M interface entries and sorting them on the host took 15 ms.
+//   list 0 (send):  item v = (k, c) = (v / len_me, begin[me] + v % len_me);  kept if k != me and rank k reads c
+//   list 1 (recv):  item v = c, k = owner(c);                                  kept if k != me and I read c
+// Both come out ordered by (peer, column), the same order on the sending and on the receiving rank.
+__device__ __forceinline__ bool halo_item(int list, const RowPart &part, int me, int64_t v, const uint32_t *needmask,
+                                          int32_t &c) {
+    if (list == 0) {
+        const int64_t len = part.begin[me + 1] - part.begin[me];
+        const int k = (int)(v / len);
+        c = (int32_t)(part.begin[me] + (v - (int64_t)k * len));
+        return k != me && ((needmask[c] >> k) & 1u);
     }
+    c = (int32_t)v;
+    return part.owner(v) != me && ((needmask[c] >> me) & 1u);
+}
+__global__ void __launch_bounds__(256) halo_flag_kernel(int list, RowPart part, int me, int64_t n_items,
+                                                        const uint32_t *__restrict__ needmask, int32_t *__restrict__ flag) {
+    for (int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x; v < n_items; v += (int64_t)gridDim.x * 256) {
+        int32_t c;
+        flag[v] = halo_item(list, part, me, v, needmask, c) ? 1 : 0;
+    }
+}
+__global__ void __launch_bounds__(256) halo_scatter_kernel(int list, RowPart part, int me, int64_t n_items,
+                                                           const uint32_t *__restrict__ needmask,
+                                                           const int32_t *__restrict__ offs, int32_t *__restrict__ out) {
+    for (int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x; v < n_items; v += (int64_t)gridDim.x * 256) {
+        int32_t c;
+        if (halo_item(list, part, me, v, needmask, c)) out[offs[v]] = c;
+    }
+}
+// first list position of every peer: out[k] (send), out[world + 1 + k] (recv), k = 0 .. world
+__global__ void halo_offsets_kernel(RowPart part, int me, const int32_t *__restrict__ offs_send,
+                                    const int32_t *__restrict__ offs_recv, int32_t *__restrict__ out) {
+    const int k = threadIdx.x;
+    if (k > part.world) return;
+    const int64_t len = part.begin[me + 1] - part.begin[me];
+    out[k] = offs_send[(int64_t)k * len];
+    out[part.world + 1 + k] = offs_recv[part.begin[k]];
 }
 
 static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/) {
@@ -867,52 +910,50 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     PDN_CUDA(cudaMemsetAsync(w->needmask.p, 0, (size_t)n * sizeof(uint32_t), st));
     PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
                w->needmask.p);
-    w->tmp_i32a.reserve(4);
-    int32_t cnt = 0;
-    PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, sizeof(int32_t), st));
-    PDN_LAUNCH(ctx, halo_collect_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->needmask.p, 0, w->tmp_i32a.p,
-               (int32_t *)nullptr, (int32_t *)nullptr);
-    PDN_CUDA(cudaMemcpyAsync(&cnt, w->tmp_i32a.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    PDN_CUDA(cudaStreamSynchronize(st));
-    std::vector<std::pair<int32_t, uint32_t>> marked((size_t)cnt);
-    if (cnt > 0) {
-        w->halo_col.reserve((size_t)cnt);
-        w->halo_mask.reserve((size_t)cnt);
-        PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, sizeof(int32_t), st));
-        PDN_LAUNCH(ctx, halo_collect_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->needmask.p, cnt, w->tmp_i32a.p,
-                   w->halo_col.p, w->halo_mask.p);
-        std::vector<int32_t> col(cnt), mask(cnt);
-        PDN_CUDA(cudaMemcpyAsync(col.data(), w->halo_col.p, cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PDN_CUDA(cudaMemcpyAsync(mask.data(), w->halo_mask.p, cnt * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        PDN_CUDA(cudaStreamSynchronize(st));
-        for (int32_t i = 0; i < cnt; i++) marked[i] = {col[i], (uint32_t)mask[i]};
-        std::sort(marked.begin(), marked.end());
+    const int64_t n_send_items = (int64_t)world * (h.begin[me + 1] - h.begin[me]), n_recv_items = n;
+    const int64_t n_items = std::max(n_send_items, n_recv_items);
+    w->tmp_i32b.reserve((size_t)n_items + 1);       // flags
+    w->halo_col.reserve((size_t)n_send_items + 1);  // offsets of the send items
+    w->halo_mask.reserve((size_t)n_recv_items + 1); // offsets of the receive items
+    w->tmp_i32a.reserve((size_t)2 * (world + 1));
+    std::vector<int32_t> offs((size_t)2 * (world + 1), 0);
+    if (n_send_items > 0) {
+        PDN_LAUNCH(ctx, halo_flag_kernel, pdn_grid(ctx, n_send_items, 256, 8), 256, 0, 0, part, me, n_send_items,
+                   w->needmask.p, w->tmp_i32b.p);
+        pdn_exclusive_scan_i32(ctx, w->tmp_i32b.p, n_send_items, w->halo_col.p);
+    } else {
+        PDN_CUDA(cudaMemsetAsync(w->halo_col.p, 0, sizeof(int32_t), st));
     }
+    PDN_LAUNCH(ctx, halo_flag_kernel, pdn_grid(ctx, n_recv_items, 256, 8), 256, 0, 1, part, me, n_recv_items,
+               w->needmask.p, w->tmp_i32b.p);
+    pdn_exclusive_scan_i32(ctx, w->tmp_i32b.p, n_recv_items, w->halo_mask.p);
+    PDN_LAUNCH(ctx, halo_offsets_kernel, 1, 32, 0, part, me, w->halo_col.p, w->halo_mask.p, w->tmp_i32a.p);
+    PDN_CUDA(cudaMemcpyAsync(offs.data(), w->tmp_i32a.p, offs.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
     h.send_off.assign(world, 0); h.send_cnt.assign(world, 0);
     h.recv_off.assign(world, 0); h.recv_cnt.assign(world, 0);
-    std::vector<int32_t> send_idx, recv_idx;
     for (int k = 0; k < world; k++) {
-        h.send_off[k] = (int32_t)send_idx.size();
-        h.recv_off[k] = (int32_t)recv_idx.size();
-        if (k == me) continue;
-        for (const auto &cm : marked) {
-            const int owner = part.owner(cm.first);
-            if (owner == me && (cm.second >> k) & 1u) send_idx.push_back(cm.first);   // peer k reads my entry
-            if (owner == k && (cm.second >> me) & 1u) recv_idx.push_back(cm.first);   // I read peer k's entry
-        }
-        h.send_cnt[k] = (int32_t)send_idx.size() - h.send_off[k];
-        h.recv_cnt[k] = (int32_t)recv_idx.size() - h.recv_off[k];
+        h.send_off[k] = offs[k];
+        h.send_cnt[k] = offs[k + 1] - offs[k];
+        h.recv_off[k] = offs[world + 1 + k];
+        h.recv_cnt[k] = offs[world + 2 + k] - offs[world + 1 + k];
     }
-    h.n_send = (int32_t)send_idx.size();
-    h.n_recv = (int32_t)recv_idx.size();
+    h.n_send = offs[world];
+    h.n_recv = offs[2 * world + 1];
     h.peer = HaloSend{};
     for (int k = 0; k < world && k < PEER_MAX; k++) {
         h.peer.off[k] = h.send_off[k];
         h.peer.cnt[k] = h.send_cnt[k];
         h.peer.recv_cnt[k] = h.recv_cnt[k];
     }
-    upload(ctx, h.send_idx, send_idx);
-    upload(ctx, h.recv_idx, recv_idx);
+    h.send_idx.reserve((size_t)h.n_send + 1);
+    h.recv_idx.reserve((size_t)h.n_recv + 1);
+    if (h.n_send > 0)
+        PDN_LAUNCH(ctx, halo_scatter_kernel, pdn_grid(ctx, n_send_items, 256, 8), 256, 0, 0, part, me, n_send_items,
+                   w->needmask.p, w->halo_col.p, h.send_idx.p);
+    if (h.n_recv > 0)
+        PDN_LAUNCH(ctx, halo_scatter_kernel, pdn_grid(ctx, n_recv_items, 256, 8), 256, 0, 1, part, me, n_recv_items,
+                   w->needmask.p, w->halo_mask.p, h.recv_idx.p);
     h.sendbuf.reserve((size_t)h.n_send + 1);
     h.recvbuf.reserve((size_t)h.n_recv + 1);
 }
@@ -1047,9 +1088,35 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     return true;
 }
 
+// PADNE_B200_TRACE=1: wall-clock per phase of one solve (each mark drains the stream, so the phases add
+// up to more than an untraced solve); printed to stderr by every rank
+struct PhaseTrace {
+    bool on;
+    cudaStream_t st;
+    int rank;
+    std::chrono::steady_clock::time_point t0;
+    std::string out;
+    PhaseTrace(cudaStream_t s, int r) : on(getenv("PADNE_B200_TRACE") != nullptr), st(s), rank(r) {
+        if (on) { cudaStreamSynchronize(st); t0 = std::chrono::steady_clock::now(); }
+    }
+    void mark(const char *name) {
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        const auto t1 = std::chrono::steady_clock::now();
+        char buf[96];
+        snprintf(buf, sizeof buf, " %s=%.3f", name, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        out += buf;
+        t0 = t1;
+    }
+    ~PhaseTrace() {
+        if (on) fprintf(stderr, "[padne_b200 trace rank %d]%s (ms)\n", rank, out.c_str());
+    }
+};
+
 void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, double *v_out, pdn_info *info,
                     bool on_device) {
     cudaStream_t st = ctx->stream;
+    PhaseTrace trace(st, pdn_comm_rank(ctx));
     SolveWork *w = get_work(ctx);
     const CsrDev &L = ctx->L;
     const int64_t N = L.n;
@@ -1142,6 +1209,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         }
     }
 
+    trace.mark("border");
     // ---- elimination ------------------------------------------------------------------------------
     Elim E;
     build_elim(E, n, N, c_ptr, c_col, c_val, b_row, b_col, b_val, rhs_tail.data());
@@ -1151,6 +1219,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     if (method == PDN_METHOD_PCG && !E.symmetric)
         PDN_FAIL(PDN_EINVAL, "solve: PCG requested but the regulator coupling makes the system non-symmetric");
 
+    trace.mark("elim_host");
     // map / offsets on the device
     w->map.reserve((size_t)n);
     w->off.reserve((size_t)N);
@@ -1195,6 +1264,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
                L.data.p, w->map.p, w->special.p, w->perm.p, w->inv.p, w->soff.p, w->s_ci.p, w->s_va.p, w->smask.p,
                w->dinv.p);
 
+    trace.mark("sell");
     // g = r_n - L_nn o
     w->full_a.reserve((size_t)N);
     w->full_b.reserve((size_t)N);
@@ -1304,6 +1374,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     w->A.sp_rp = w->sp_rp.p;
     w->A.sp_ci = w->sp_ci.p;
     w->A.sp_va = w->sp_va.p;
+    trace.mark("override_rows");
     // rows of the Krylov loop this rank owns: whole sort windows, split evenly
     {
         const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
@@ -1319,6 +1390,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         if (world > 1) build_halo_plan(ctx, w, (int32_t)r_ci.size());
     }
     w->have_operator = true;
+    trace.mark("halo_plan");
 
     // second level of the preconditioner (systems assembled from meshes: the aggregates are coordinate bins)
     w->two_level = false;
@@ -1351,6 +1423,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         }
     }
 
+    trace.mark("coarse");
     // vectors.  The SpMV inputs (z, ph, sh, x) are the halo-exchanged ones: with peer-memory exchanges
     // they live in the arena every peer has mapped
     {
@@ -1370,10 +1443,12 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         w->ph.reserve((size_t)n); w->tt.reserve((size_t)n);
     }
     PDN_CUDA(cudaEventRecord(ev_setup, st));
+    trace.mark("vectors");
 
     // ---- Krylov -------------------------------------------------------------------------------------
     KrylovResult kr = run_krylov(ctx, w, method, rtol, atol, max_iter, check_every);
 
+    trace.mark("krylov");
     if (is_dist(ctx)) {   // a peer that never answered (pdn_peer.cuh deadline)
         int64_t detail = 0;
         const int stt = pdn_status_fetch(ctx, &detail);

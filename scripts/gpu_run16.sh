@@ -1,0 +1,15 @@
+mkdir -p gpurun_out
+for lib in "" _evict; do
+echo "== lib$lib"
+PADNE_B200_LIB=$PWD/padne_b200/_lib/libpadne_b200$lib.so timeout 600 python profiles/precond_sweep.py 2layer_1M full 1600 2>&1 | python -c "
+import sys,json
+for l in sys.stdin:
+    try: d=json.loads(l)
+    except Exception: print(l[:200]); continue
+    print({k:d.get(k) for k in ('precond','n_coarse','iterations','t_krylov_ms','t_total_ms','us_per_iteration','error')})"
+PADNE_B200_LIB=$PWD/padne_b200/_lib/libpadne_b200$lib.so timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
+import sys,json
+for l in sys.stdin:
+    if not l.startswith('{'): continue
+    d=json.loads(l); r=d['roofline']; print('value',round(d['value']/1e6,2),'ms/step',round(d['ms_per_step'],2),'e2e',round(d['e2e']['value']/1e6,2),'frac',round(r['frac'],3),'insitu',r['ms_per_launch_in_situ'],'warm',r['ms_per_launch_warm_l2'],'cold',r['ms_per_launch_cold_l2'])"
+done
