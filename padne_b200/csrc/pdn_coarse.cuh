@@ -25,7 +25,7 @@ constexpr int CO_BLK = 256;
 constexpr double CO_RFIX = 1099511627776.0;   // 2^40: fixed-point steps per ||r|| in the restriction
 // PCG restricts with 32-bit fixed point (one redux.sync instead of three, a fraction of the integer work:
 // cg_update_kernel<TL> was instruction-issue bound, ~250 instructions per 32 rows).  2^22 steps per ||r_k||,
-// entries clamped to +-(2^26 - 1) so that 32 lanes cannot overflow: 16x headroom for a residual that grows in
+// entries clamped so that 32 lanes (of one or two rows each) cannot overflow: 8-16x headroom for a residual that grows in
 // one step.  The quantisation (2.4e-7 ||r|| per entry) only perturbs the preconditioner.
 #ifndef PDN_RESTRICT_WIDE
 #define PDN_RESTRICT_WIDE 0
@@ -208,12 +208,12 @@ __device__ __forceinline__ bool flag_wait(const unsigned int *flag, int32_t *sta
 
 // out_i,j = sum_q c[i][q] * P_q,j for four columns per thread at a time: the 16 x 4 operand block sits
 // in registers, every multiplier is read from shared memory once per four columns (one LDS per FMA made
-// both phases LDS-bound: 22 us per block step).
-//   OWNER:  P = my old rows, A_i,j <- out (j not in K) | c[i][j-k0] (j in K), also stored to pb
-//   else:   P = pb (published pivot rows),  A_i,j <- (j in K ? 0 : A_i,j) - out
+// both phases LDS-bound).
+//   OWNER:  P = my old rows, c = D^-1:        A_K,j <- out (j not in K) | c[i][j-k0] (j in K)
+//   else:   P = pb (the owner's OLD rows), c = A_iK D^-1:  A_i,j <- A_i,j - out (j not in K) | -c[i][j-k0] (j in K)
 template <bool OWNER>
-__device__ __forceinline__ void co_rank_update(double *rows, const double (*cs)[16], double *pb, int nc, int ni, int nk,
-                                               int k0) {
+__device__ __forceinline__ void co_rank_update(double *rows, const double (*cs)[16], const double *pb, int nc, int ni,
+                                               int nk, int k0) {
     const int tid = threadIdx.x;
     for (int j0 = tid; j0 < nc; j0 += 4 * CO_BLK) {
         double p[4][16];
@@ -237,33 +237,34 @@ __device__ __forceinline__ void co_rank_update(double *rows, const double (*cs)[
                 const int j = j0 + t * CO_BLK;
                 if (j >= nc) continue;
                 const bool in_k = j >= k0 && j < k0 + nk;
-                if (OWNER) {
-                    const double o = in_k ? cs[i][j - k0] : acc[t];
-                    rows[i * nc + j] = o;
-                    pb[i * nc + j] = o;
-                } else {
-                    rows[i * nc + j] = (in_k ? 0.0 : rows[i * nc + j]) - acc[t];
-                }
+                if (OWNER) rows[i * nc + j] = in_k ? cs[i][j - k0] : acc[t];
+                else rows[i * nc + j] = in_k ? -cs[i][j - k0] : rows[i * nc + j] - acc[t];
             }
         }
     }
 }
 
+// piv[kb]: the owner's rows BEFORE the multiplication by D^-1 (R * nc doubles), then D^-1 (16 x 16).
+// Publishing the old rows lets every other CTA start its update while the owner still multiplies its own
+// rows: the serial chain per block step is (update my rows, invert D, publish), not (..., multiply, publish).
 __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, int32_t R, double *__restrict__ A,
-                                                                  double *__restrict__ piv /*[n_blk][R * nc]*/,
-                                                                  unsigned int *flags /*[n_blk], zeroed*/, int32_t *status) {
+                                                                  double *__restrict__ piv /*[n_blk][R * nc + 256]*/,
+                                                                  unsigned int *flags /*[n_blk], zeroed*/, int32_t *status,
+                                                                  float *__restrict__ Af /* the inverse in fp32 */) {
     extern __shared__ double rows[];                 // [R][nc]
-    __shared__ __align__(16) double cs[16][16];      // D, then D^-1 (owner) / multipliers (others); R <= 16
+    __shared__ __align__(16) double cs[16][16];      // D^-1 (owner) / A_iK D^-1 (others); R <= 16
+    __shared__ __align__(16) double dv[16][16], ak[16][16];
     const int b = blockIdx.x, tid = threadIdx.x;
     const int r0 = b * R;
     const int nr = r0 >= nc ? 0 : (r0 + R <= nc ? R : nc - r0);
     for (int e = tid; e < nr * nc; e += CO_BLK) rows[e] = A[(size_t)r0 * nc + e];
     __syncthreads();
     const int n_blk = (nc + R - 1) / R;
-    const int di = tid >> 4, dj = tid & 15;          // CO_BLK == 256: one thread per entry of cs
+    const size_t pstride = (size_t)R * nc + 256;
+    const int di = tid >> 4, dj = tid & 15;          // CO_BLK == 256: one thread per entry of a 16 x 16 block
     for (int kb = 0; kb < n_blk; kb++) {
         const int k0 = kb * R, nk = k0 + R <= nc ? R : nc - k0;
-        double *pb = piv + (size_t)kb * R * nc;
+        double *pb = piv + (size_t)kb * pstride;
         if (kb == b) {
             // D^-1 in place (identity padding beyond nk)
             cs[di][dj] = (di < nk && dj < nk) ? rows[di * nc + k0 + dj] : (di == dj ? 1.0 : 0.0);
@@ -277,19 +278,33 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
                 cs[di][dj] = di == q ? pr : (dj == q ? 0.0 : cur) - cq * pr;
             }
             __syncthreads();
-            co_rank_update<true>(rows, cs, pb, nc, nk, nk, k0);
+            for (int e = tid; e < nk * nc; e += CO_BLK) pb[e] = rows[e];
+            pb[(size_t)R * nc + tid] = cs[di][dj];
             __threadfence();
             __syncthreads();
             if (tid == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flags + kb), "r"(1u) : "memory");
+            co_rank_update<true>(rows, cs, nullptr, nc, nk, nk, k0);
+            __syncthreads();
         } else {
             if (!flag_wait(flags + kb, status)) return;
-            cs[di][dj] = (di < nr && dj < nk) ? rows[di * nc + k0 + dj] : 0.0;
+            dv[di][dj] = __ldcg(&pb[(size_t)R * nc + tid]);
+            ak[di][dj] = (di < nr && dj < nk) ? rows[di * nc + k0 + dj] : 0.0;
+            __syncthreads();
+            double c = 0.0;
+#pragma unroll
+            for (int q = 0; q < 16; q++) c += ak[di][q] * dv[q][dj];
+            cs[di][dj] = c;
             __syncthreads();
             co_rank_update<false>(rows, cs, pb, nc, nr, nk, k0);
             __syncthreads();
         }
     }
-    for (int e = tid; e < nr * nc; e += CO_BLK) A[(size_t)r0 * nc + e] = rows[e];
+    // the iteration applies the inverse from an fp32 copy (half the L2 traffic of the latency-bound
+    // coarse_apply_kernel; a 6e-8 relative perturbation of a preconditioner)
+    for (int e = tid; e < nr * nc; e += CO_BLK) {
+        A[(size_t)r0 * nc + e] = rows[e];
+        Af[(size_t)r0 * nc + e] = (float)rows[e];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -303,7 +318,7 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 // block reduction of CO_RB sums in a fixed order.
 constexpr int CO_RB = 4;
 constexpr int CO_JMAX = (CO_MAX + CO_BLK - 1) / CO_BLK;   // columns per thread
-__global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const double *__restrict__ Ainv, const Scal *__restrict__ sc,
+__global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const float *__restrict__ Ainv, const Scal *__restrict__ sc,
                                                               long long *__restrict__ rc_fix, double *__restrict__ xc,
                                                               int slot, double boost) {
     __shared__ double rcd[CO_MAX];
@@ -311,14 +326,16 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int row0 = blockIdx.x * CO_RB;
     // the matrix entries do not depend on anything this iteration produced: request them first
-    double a[CO_RB][CO_JMAX];
+    float a[CO_RB][CO_JMAX];
 #pragma unroll
     for (int q = 0; q < CO_RB; q++)
 #pragma unroll
         for (int t = 0; t < CO_JMAX; t++) {
             const int j = tid + t * CO_BLK;
-            a[q][t] = (row0 + q < nc && j < nc) ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.0;
+            a[q][t] = (row0 + q < nc && j < nc) ? __ldg(&Ainv[(size_t)(row0 + q) * nc + j]) : 0.f;
         }
+    pdl_trigger();
+    pdl_wait();                 // the inverse is setup data; everything below depends on the update kernel
     if (sc->done) return;
     const int par = slot < 0 ? (sc->iter & 1) : slot;
     const long long *__restrict__ rc = rc_fix + (size_t)par * nc;
@@ -333,7 +350,7 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const 
 #pragma unroll
         for (int t = 0; t < CO_JMAX; t++) {
             const int j = tid + t * CO_BLK;
-            if (j < nc) acc[q] = fma(a[q][t], rcd[j], acc[q]);
+            if (j < nc) acc[q] = fma((double)a[q][t], rcd[j], acc[q]);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_down_sync(0xffffffffu, acc[q], o);
@@ -348,15 +365,27 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const 
     }
 }
 
-// z = D^-1 r + P x_c  over the rows [r0, n)
+// z = D^-1 r + P x_c  over the rows [r0, n); two rows per thread (r0 is even, the vectors are 16 B aligned)
 __global__ void __launch_bounds__(CO_BLK) coarse_z_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                           const double *__restrict__ dinv, const double *__restrict__ r,
                                                           const int32_t *__restrict__ agg, const double *__restrict__ xc,
                                                           double *__restrict__ z) {
+    pdl_trigger();
+    pdl_wait();
     if (sc->done) return;
-    for (int64_t i = r0 + (int64_t)blockIdx.x * CO_BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * CO_BLK) {
-        const int32_t a = agg[i];
-        z[i] = dinv[i] * r[i] + (a >= 0 ? __ldg(&xc[a]) : 0.0);
+    const int64_t npair = (n - r0 + 1) >> 1;
+    for (int64_t t = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; t < npair; t += (int64_t)gridDim.x * CO_BLK) {
+        const int64_t i = r0 + 2 * t;
+        if (i + 1 < n) {
+            const double2 dd = *reinterpret_cast<const double2 *>(dinv + i), rr = *reinterpret_cast<const double2 *>(r + i);
+            const int2 aa = *reinterpret_cast<const int2 *>(agg + i);
+            const double ca = aa.x >= 0 ? __ldg(&xc[aa.x]) : 0.0;
+            const double cb = aa.y == aa.x ? ca : (aa.y >= 0 ? __ldg(&xc[aa.y]) : 0.0);
+            *reinterpret_cast<double2 *>(z + i) = make_double2(dd.x * rr.x + ca, dd.y * rr.y + cb);
+        } else {
+            const int32_t a = agg[i];
+            z[i] = dinv[i] * r[i] + (a >= 0 ? __ldg(&xc[a]) : 0.0);
+        }
     }
 }
 
@@ -370,6 +399,31 @@ __device__ __forceinline__ void restrict_add_narrow(double ri, int32_t a, double
     const int sum = __reduce_add_sync(peers, q);
     if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && a >= 0 && sum != 0)
         atomicAdd(&rc[a], (unsigned long long)(long long)sum);
+}
+__device__ __forceinline__ void restrict_add(double ri, int32_t a, double fix, unsigned long long *rc);
+// two rows per lane (cg_update_kernel): entries clamped to +-(2^25 - 1), equal aggregates are summed in the
+// lane, the second collective round only runs when some lane straddles two aggregates
+__device__ __forceinline__ void restrict_add_pair(double ra, int32_t a0, double rb, int32_t a1, double fix,
+                                                  unsigned long long *rc) {
+#if PDN_RESTRICT_WIDE
+    restrict_add(ra, a0, fix, rc);
+    restrict_add(rb, a1, fix, rc);
+#else
+    int q0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
+    int q1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
+    if (a1 == a0) { q0 += q1; a1 = -1; }
+    const int lane = threadIdx.x & 31;
+    {
+        const unsigned peers = __match_any_sync(0xffffffffu, a0);
+        const int sum = __reduce_add_sync(peers, q0);
+        if (lane == __ffs(peers) - 1 && a0 >= 0 && sum != 0) atomicAdd(&rc[a0], (unsigned long long)(long long)sum);
+    }
+    if (__any_sync(0xffffffffu, a1 >= 0)) {
+        const unsigned peers = __match_any_sync(0xffffffffu, a1);
+        const int sum = __reduce_add_sync(peers, q1);
+        if (lane == __ffs(peers) - 1 && a1 >= 0 && sum != 0) atomicAdd(&rc[a1], (unsigned long long)(long long)sum);
+    }
+#endif
 }
 __device__ __forceinline__ void restrict_add(double ri, int32_t a, double fix, unsigned long long *rc) {
     const double lim = 72057594037927935.0;   // 2^56 - 1

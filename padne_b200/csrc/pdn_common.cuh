@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <utility>
 
 #include <string>
 #include <vector>
@@ -137,6 +138,35 @@ struct pdn_ctx {
         (ctx)->launches++;                                                                      \
         PDN_CUDA(cudaGetLastError());                                                           \
     } while (0)
+
+// Programmatic dependent launch (PDL): the kernel may be scheduled while its predecessor in the stream is
+// still draining, which hides most of the ~2 us kernel boundary inside the Krylov graph.  Such a kernel calls
+// pdl_wait() before it touches anything the predecessor wrote (everything before the wait must be
+// independent of it) and pdl_trigger() to let its own successor be scheduled early.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+static inline cudaError_t pdn_launch_ex(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                        bool pdl, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+#define PDN_LAUNCH_PDL(ctx, pdl, kernel, grid, block, smem, ...)                                              \
+    do {                                                                                                      \
+        PDN_CUDA(pdn_launch_ex(kernel, dim3(grid), dim3(block), (size_t)(smem), (ctx)->stream, (pdl), __VA_ARGS__)); \
+        (ctx)->launches++;                                                                                    \
+    } while (0)
+#endif
 
 static inline int pdn_blocks(int64_t n, int block) { return (int)((n + block - 1) / block); }
 

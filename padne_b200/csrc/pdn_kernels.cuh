@@ -154,6 +154,12 @@ __global__ void scalar_kernel(Scal *sc, double *out) {
 // Chronopoulos-Gear update:  p = z + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  z = dinv r
 // TL (two-level preconditioner): z is produced later by coarse_z_kernel; here the new residual is
 // restricted onto the aggregates, r_c[agg] += r (fixed point, pdn_coarse.cuh).
+// Two rows per thread (128-bit loads and stores, half the address arithmetic and half the warp collectives
+// of the restriction): the one-row version was instruction-issue bound (~250 instructions per 32 rows) once
+// the vectors stayed in L2.  r0 is a multiple of the sort window, so row pairs are the same on every rank count.
+__device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
+__device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
+
 template <bool TL>
 __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                         const double *__restrict__ dinv,
@@ -161,28 +167,131 @@ __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, c
                                                         double *__restrict__ p, double *__restrict__ s,
                                                         double *__restrict__ x, double *__restrict__ r,
                                                         const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
+    pdl_trigger();
+    pdl_wait();
     if (sc->done) return;
     const double alpha = sc->alpha, beta = sc->beta;
     const double fix = TL ? CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300)) : 0.0;
     unsigned long long *rc = TL ? reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc : nullptr;
-    for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
-        const int64_t i = i0 + threadIdx.x;
-        const bool act = i < n;
-        double ri = 0.0;
-        if (act) {
+    const int64_t npair = (n - r0 + 1) >> 1;
+    for (int64_t t0 = (int64_t)blockIdx.x * RPB; t0 < npair; t0 += (int64_t)gridDim.x * RPB) {
+        const int64_t t = t0 + threadIdx.x;
+        const int64_t i = r0 + 2 * t;
+        const bool act = t < npair, full = act && i + 1 < n;
+        double ra = 0.0, rb = 0.0;
+        if (full) {
+            const double2 zz = ld2(z + i), pp = ld2(p + i), ww = ld2(w + i), ss = ld2(s + i), rr = ld2(r + i), xx = ld2(x + i);
+            const double pa = zz.x + beta * pp.x, pb = zz.y + beta * pp.y;
+            const double sa = ww.x + beta * ss.x, sb = ww.y + beta * ss.y;
+            ra = rr.x - alpha * sa;
+            rb = rr.y - alpha * sb;
+            st2(p + i, pa, pb);
+            st2(s + i, sa, sb);
+            st2(x + i, xx.x + alpha * pa, xx.y + alpha * pb);
+            st2(r + i, ra, rb);
+            if (!TL) {
+                const double2 dd = ld2(dinv + i);
+                st2(z + i, dd.x * ra, dd.y * rb);
+            }
+        } else if (act) {
             const double pi = z[i] + beta * p[i];
             const double si = w[i] + beta * s[i];
-            ri = r[i] - alpha * si;
+            ra = r[i] - alpha * si;
             p[i] = pi;
             s[i] = si;
             x[i] += alpha * pi;
-            r[i] = ri;
-            if (!TL) z[i] = dinv[i] * ri;
+            r[i] = ra;
+            if (!TL) z[i] = dinv[i] * ra;
         }
         if (TL) {
-            if (PDN_RESTRICT_WIDE) restrict_add(ri, act ? agg[i] : -1, fix, rc);
-            else restrict_add_narrow(ri, act ? agg[i] : -1, fix, rc);
+            int32_t a0 = -1, a1 = -1;
+            if (full) {
+                const int2 aa = *reinterpret_cast<const int2 *>(agg + i);
+                a0 = aa.x;
+                a1 = aa.y;
+            } else if (act) {
+                a0 = agg[i];
+            }
+            restrict_add_pair(ra, a0, rb, a1, fix, rc);
         }
+    }
+}
+
+// The two-level update: as above without z, plus the restriction of the new residual.  One global atomic per
+// (warp, aggregate) -- 62K of them onto ~90 cache lines at 1M rows -- cost more than the whole vector update,
+// so every CTA owns a CONTIGUOUS range of row pairs (few aggregates), sums them in a shared-memory table and
+// flushes its non-zero entries at the end: ~2K global atomics per launch.  1024 threads per CTA, two CTAs per
+// SM, so that the table is cleared and flushed by two entries per thread.
+constexpr int TLB = 1024;
+__global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
+                                                              const double *__restrict__ w, const double *__restrict__ z,
+                                                              double *__restrict__ p, double *__restrict__ s,
+                                                              double *__restrict__ x, double *__restrict__ r,
+                                                              const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc) {
+    __shared__ long long tab[CO_MAX];
+    pdl_trigger();
+    for (int a = threadIdx.x; a < nc; a += TLB) tab[a] = 0;
+    pdl_wait();
+    if (sc->done) return;
+    const double alpha = sc->alpha, beta = sc->beta;
+    const double fix = CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300));
+    unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc;
+    const int64_t npair = (n - r0 + 1) >> 1;
+    const int64_t per = ((npair + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;   // whole warps
+    const int64_t t_lo = (int64_t)blockIdx.x * per, t_hi = t_lo + per < npair ? t_lo + per : npair;
+    const int lane = threadIdx.x & 31;
+    __syncthreads();    // table cleared
+    for (int64_t t0 = t_lo; t0 < t_hi; t0 += TLB) {
+        const int64_t t = t0 + threadIdx.x;
+        const int64_t i = r0 + 2 * t;
+        const bool act = t < t_hi, full = act && i + 1 < n;
+        double ra = 0.0, rb = 0.0;
+        int32_t a0 = -1, a1 = -1;
+        if (full) {
+            const double2 zz = ld2(z + i), pp = ld2(p + i), ww = ld2(w + i), ss = ld2(s + i), rr = ld2(r + i);
+            const double2 xx = __ldcs(reinterpret_cast<const double2 *>(x + i));   // x is touched once per iteration
+            const int2 aa = *reinterpret_cast<const int2 *>(agg + i);
+            const double pa = zz.x + beta * pp.x, pb = zz.y + beta * pp.y;
+            const double sa = ww.x + beta * ss.x, sb = ww.y + beta * ss.y;
+            ra = rr.x - alpha * sa;
+            rb = rr.y - alpha * sb;
+            st2(p + i, pa, pb);
+            st2(s + i, sa, sb);
+            __stcs(reinterpret_cast<double2 *>(x + i), make_double2(xx.x + alpha * pa, xx.y + alpha * pb));
+            st2(r + i, ra, rb);
+            a0 = aa.x;
+            a1 = aa.y;
+        } else if (act) {
+            const double pi = z[i] + beta * p[i];
+            const double si = w[i] + beta * s[i];
+            ra = r[i] - alpha * si;
+            p[i] = pi;
+            s[i] = si;
+            x[i] += alpha * pi;
+            r[i] = ra;
+            a0 = agg[i];
+        }
+        // warp-level sums per aggregate, then one shared-memory add per (warp, aggregate)
+        int q0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
+        int q1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
+        if (a1 == a0) { q0 += q1; a1 = -1; }
+        {
+            const unsigned peers = __match_any_sync(0xffffffffu, a0);
+            const int sum = __reduce_add_sync(peers, q0);
+            if (lane == __ffs(peers) - 1 && a0 >= 0 && sum != 0)
+                atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a0]), (unsigned long long)(long long)sum);
+        }
+        if (__any_sync(0xffffffffu, a1 >= 0)) {
+            const unsigned peers = __match_any_sync(0xffffffffu, a1);
+            const int sum = __reduce_add_sync(peers, q1);
+            if (lane == __ffs(peers) - 1 && a1 >= 0 && sum != 0)
+                atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a1]), (unsigned long long)(long long)sum);
+        }
+    }
+    __syncthreads();
+    for (int a = threadIdx.x; a < nc; a += TLB) {
+        const long long v = tab[a];
+        if (v != 0) atomicAdd(&rc[a], (unsigned long long)v);
     }
 }
 

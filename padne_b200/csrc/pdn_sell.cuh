@@ -225,6 +225,8 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
                                                                      const double *__restrict__ aux0, Scal *sc,
                                                                      double *partials) {
     extern __shared__ __align__(128) unsigned char st_smem[];
+    pdl_trigger();
+    pdl_wait();
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }

@@ -156,11 +156,13 @@ struct SolveWork {
     int32_t n_special = 0;
     // two-level preconditioner (pdn_coarse.cuh)
     bool two_level = false;
+    bool pdl = false;          // programmatic dependent launches inside the captured PCG iterations (one GPU)
     int32_t nc = 0;
     float coarse_ms = 0.f;
     DevBuf<int32_t> agg, co_used, co_cid;
     DevBuf<long long> co_acc, rc_fix;
     DevBuf<double> co_A, co_piv, xc, co_tmp;
+    DevBuf<float> co_Af;
     DevBuf<unsigned int> co_counter;
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
@@ -249,7 +251,7 @@ static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, doub
     }
     int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
     grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + ST_WARPS - 1) / ST_WARPS));
-    PDN_LAUNCH(ctx, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p);
+    PDN_LAUNCH_PDL(ctx, w->pdl, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p);
 #else
     auto kern = sell_spmv_kernel<MODE, DIST>;
     static int per_sm = 0;
@@ -580,9 +582,10 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
             pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
     }
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
-    PDN_LAUNCH(ctx, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_A.p, w->d_sc, w->rc_fix.p, w->xc.p, slot, boost);
-    PDN_LAUNCH(ctx, coarse_z_kernel, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src, w->agg.p,
-               w->xc.p, dst);
+    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_fix.p, w->xc.p, slot,
+                   boost);
+    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_z_kernel, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src,
+                   w->agg.p, w->xc.p, dst);
 }
 
 void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
@@ -590,11 +593,18 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     halo_exchange(ctx, w, w->z.p);
     launch_sell<CG>(ctx, w, w->z.p, w->w.p, w->r.p);
     if (w->two_level) {
-        PDN_LAUNCH(ctx, cg_update_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
-                   w->x.p, w->r.p, w->agg.p, w->rc_fix.p, w->nc);
+        const int64_t npair = (r1 - r0 + 1) / 2;
+        static int tl_per_sm = 0;
+        if (!tl_per_sm) {
+            PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&tl_per_sm, cg_update_tl_kernel, TLB, 0));
+            if (tl_per_sm < 1) tl_per_sm = 1;
+        }
+        const int tgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * tl_per_sm, (npair + TLB - 1) / TLB));
+        PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_tl_kernel, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
+                       w->r.p, w->agg.p, w->rc_fix.p, w->nc);
         enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p);
     } else {
-        PDN_LAUNCH(ctx, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
+        PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                    w->x.p, w->r.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
     }
 }
@@ -688,6 +698,9 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     cudaGraphExec_t exec = nullptr;
     auto build_graph = [&]() {
         const int64_t launches_before = ctx->launches;
+        // PCG on one GPU: the four kernels of an iteration are chained by programmatic dependent launches
+        const char *pdl_env = getenv("PADNE_B200_PDL");
+        w->pdl = method == PDN_METHOD_PCG && !dist && !(pdl_env && pdl_env[0] == '0');
         PDN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         try {
             for (int k = 0; k < check_every; k++) {
@@ -695,11 +708,13 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 else enqueue_bicg_iteration(ctx, w, vgrid);
             }
         } catch (...) {
+            w->pdl = false;
             cudaGraph_t g2 = nullptr;
             cudaStreamEndCapture(st, &g2);
             if (g2) cudaGraphDestroy(g2);
             throw;
         }
+        w->pdl = false;
         PDN_CUDA(cudaStreamEndCapture(st, &graph));
         PDN_CUDA(cudaGraphInstantiate(&exec, graph, 0));
         ctx->launches = launches_before;  // capture is not execution
@@ -1051,6 +1066,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     // rows per CTA: the critical path is one R x R inverse + one rank-R update + one flag hand-over per
     // block step, so blocks are as tall as shared memory allows
     int32_t R = (int32_t)std::min<int64_t>(16, (int64_t)(200 * 1024) / ((int64_t)nc * 8));
+    if (const char *e = getenv("PADNE_B200_CO_R")) R = std::min<int32_t>(R, std::max(1, atoi(e)));   // tuning
     R = std::max(R, (nc + ctx->n_sm - 1) / ctx->n_sm);
     if (R < 1 || R > 16) return false;
     const int grid = (nc + R - 1) / R;
@@ -1061,7 +1077,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         smem_set = 220 * 1024;
     }
     if (smem > 220 * 1024) return false;
-    w->co_piv.reserve((size_t)grid * R * nc);
+    w->co_piv.reserve((size_t)grid * ((size_t)R * nc + 256));
     w->co_counter.reserve((size_t)grid + 4);
     PDN_CUDA(cudaMemsetAsync(w->co_counter.p, 0, ((size_t)grid + 4) * sizeof(unsigned int), st));
     pdn_status_reset(ctx);
@@ -1070,7 +1086,9 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         double *A_arg = w->co_A.p, *piv_arg = w->co_piv.p;
         unsigned int *cnt_arg = w->co_counter.p;
         int32_t *st_arg = ctx->d_status;
-        void *args[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg};
+        w->co_Af.reserve(nc2);
+        float *af_arg = w->co_Af.p;
+        void *args[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg, &af_arg};
         PDN_CUDA(cudaLaunchCooperativeKernel((void *)coarse_invert_kernel, dim3(grid), dim3(CO_BLK), args, smem, st));
         ctx->launches++;
     }

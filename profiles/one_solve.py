@@ -16,6 +16,6 @@ st = build_stamps(fs)
 ctx = capi.Context(0)
 ctx.assemble(fs.v_off, fs.xy, fs.t_off, fs.tri, fs.conductance, fs.N, *st[:4])
 try:
-    ctx.solve(st[4], n_nodes=fs.n_nodes, max_iter=32)
+    ctx.solve(st[4], n_nodes=fs.n_nodes, max_iter=int(os.environ.get("ONE_SOLVE_ITERS", "32")))
 except capi.NotConvergedError as e:
     print("expected:", str(e)[:80])

@@ -1,0 +1,12 @@
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q -k "two_level or golden" 2>&1 | tail -3
+for R in 16 12 11; do
+echo "== R=$R"
+PADNE_B200_CO_R=$R timeout 600 python profiles/precond_sweep.py 2layer_1M full 1000 1600 2>&1 | python -c "
+import sys,json
+for l in sys.stdin:
+    try: d=json.loads(l)
+    except Exception: print(l[:200]); continue
+    if d.get('precond')=='jacobi': continue
+    print({k:d.get(k) for k in ('precond','n_coarse','iterations','t_krylov_ms','t_coarse_ms','t_total_ms','us_per_iteration','error')})"
+done
