@@ -108,7 +108,23 @@ struct SolveWork;     // pdn_solve.cu
 struct AssembleWork;  // pdn_assemble.cu (scratch buffers kept between calls)
 struct PdnComm;       // pdn_multi.cu
 
+// PADNE_B200_KTIME=1: the Krylov loop runs its first graph-worth of iterations eagerly with an event after
+// every launch and prints mean event-to-event times per kernel and rank (multi-rank runs cannot use ncu).
+// Short kernels are launch-bound in eager mode: the numbers locate a slow kernel, they are not a profile.
+struct KernelTimes {
+    std::vector<std::pair<const char *, cudaEvent_t>> marks;
+    bool active = false;
+    void mark(const char *name, cudaStream_t st) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, st);
+        marks.emplace_back(name, e);
+    }
+    void report(int rank);
+};
+
 struct pdn_ctx {
+    KernelTimes *ktime = nullptr;
     int device = 0;
     cudaStream_t stream = nullptr;
     int n_sm = 148;
@@ -137,6 +153,7 @@ struct pdn_ctx {
         kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                        \
         (ctx)->launches++;                                                                      \
         PDN_CUDA(cudaGetLastError());                                                           \
+        if ((ctx)->ktime && (ctx)->ktime->active) (ctx)->ktime->mark(#kernel, (ctx)->stream);   \
     } while (0)
 
 // Programmatic dependent launch (PDL): the kernel may be scheduled while its predecessor in the stream is
@@ -165,6 +182,7 @@ static inline cudaError_t pdn_launch_ex(void (*kernel)(KArgs...), dim3 grid, dim
     do {                                                                                                      \
         PDN_CUDA(pdn_launch_ex(kernel, dim3(grid), dim3(block), (size_t)(smem), (ctx)->stream, (pdl), __VA_ARGS__)); \
         (ctx)->launches++;                                                                                    \
+        if ((ctx)->ktime && (ctx)->ktime->active) (ctx)->ktime->mark(#kernel, (ctx)->stream);                 \
     } while (0)
 #endif
 
@@ -239,6 +257,7 @@ constexpr size_t PDN_PA_RC_VAL = 128;                               // [2][PEER_
 constexpr size_t PDN_PA_VEC = PDN_PA_RC_VAL + (size_t)2 * PDN_PEER_MAX * PDN_PA_RC_SLOT;   // [4][n_cap]
 constexpr int PDN_PA_NVEC = 4;            // halo-exchanged vectors living in the arena: z, ph, sh, x
 
+constexpr int PDN_PEER_LOG = 4096;          // entries of the exchange event log behind the 8 epoch words
 struct PdnPeerLink {
     int world, me;
     unsigned long long *arena[PDN_PEER_MAX];   // arena[k]: rank k's arena as mapped in this process

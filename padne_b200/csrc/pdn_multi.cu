@@ -159,6 +159,29 @@ void pdn_comm_release(pdn_ctx *ctx) {
             cudaMemcpy(h, ctx->comm->epoch, sizeof h, cudaMemcpyDeviceToHost);
             fprintf(stderr, "[padne_b200 rank %d] exchanges: halo %llu, dots %llu, coarse %llu; cycles waited: halo %llu, dots %llu, coarse %llu\n",
                     ctx->comm->rank, h[0], h[1], h[2], h[4], h[5], h[6]);
+            // event log: mean time between consecutive events (0/1 dots enter/exit, 2/3 coarse, 4/5 halo)
+            std::vector<unsigned long long> lg(PDN_PEER_LOG);
+            cudaMemcpy(lg.data(), ctx->comm->epoch + 8, lg.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+            const unsigned long long cnt = h[3], nlog = cnt < (unsigned long long)PDN_PEER_LOG ? cnt : PDN_PEER_LOG;
+            double sum[8][8] = {};
+            int num[8][8] = {};
+            for (unsigned long long q = cnt - nlog + 1; q < cnt; q++) {
+                const unsigned long long a = lg[(q - 1) & (PDN_PEER_LOG - 1)], b = lg[q & (PDN_PEER_LOG - 1)];
+                const int ea = (int)(a >> 56) & 7, eb = (int)(b >> 56) & 7;
+                const double dt = (double)((b & ((1ull << 56) - 1)) - (a & ((1ull << 56) - 1))) * 1e-3;
+                if (dt < 0 || dt > 1e4) continue;   // between solves
+                sum[ea][eb] += dt;
+                num[ea][eb]++;
+            }
+            std::string out;
+            char buf[64];
+            for (int a = 0; a < 8; a++)
+                for (int b = 0; b < 8; b++)
+                    if (num[a][b] > 16) {
+                        snprintf(buf, sizeof buf, " %d->%d %.1f us (n=%d)", a, b, sum[a][b] / num[a][b], num[a][b]);
+                        out += buf;
+                    }
+            fprintf(stderr, "[padne_b200 rank %d] event intervals:%s\n", ctx->comm->rank, out.c_str());
         }
         peer_unmap(ctx->comm);
         if (ctx->comm->epoch) cudaFree(ctx->comm->epoch);
@@ -246,8 +269,8 @@ int pdn_comm_init(pdn_ctx *ctx, int rank, int world, const void *id128) {
         const char *mode = getenv("PADNE_B200_COMM");
         c->p2p = world <= PDN_PEER_MAX && !(mode && strcmp(mode, "nccl") == 0);
         if (c->p2p) {
-            PDN_CUDA(cudaMalloc((void **)&c->epoch, 8 * sizeof(unsigned long long)));
-            PDN_CUDA(cudaMemset(c->epoch, 0, 8 * sizeof(unsigned long long)));
+            PDN_CUDA(cudaMalloc((void **)&c->epoch, (8 + PDN_PEER_LOG) * sizeof(unsigned long long)));
+            PDN_CUDA(cudaMemset(c->epoch, 0, (8 + PDN_PEER_LOG) * sizeof(unsigned long long)));
             PDN_CUDA(cudaMalloc((void **)&c->ticket, 4 * sizeof(unsigned int)));
         }
     });

@@ -16,42 +16,9 @@
 // Included by pdn_kernels.cuh (namespace pdnk).
 #pragma once
 
-constexpr int PEER_MAX = PDN_PEER_MAX;
-constexpr size_t PA_HALO_FLAG = PDN_PA_HALO_FLAG, PA_RED_FLAG = PDN_PA_RED_FLAG, PA_RC_FLAG = PDN_PA_RC_FLAG;
-constexpr size_t PA_RED_VAL = PDN_PA_RED_VAL, PA_RC_VAL = PDN_PA_RC_VAL, PA_RC_SLOT = PDN_PA_RC_SLOT;
-using PeerLink = PdnPeerLink;
-
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-// wait until *flag >= want; false (and a status word) after ~2 s
-// (the cycles spent waiting are added to *spent: PADNE_B200_PEER_STATS prints them per exchange type)
-__device__ __forceinline__ bool peer_wait(const unsigned long long *flag, unsigned long long want, int32_t *status,
-                                          unsigned long long *spent) {
-    const long long t0 = clock64();
-    bool ok = true;
-    while (ld_acquire_sys(flag) < want) {
-        if (clock64() - t0 > 4000000000LL) {
-            atomicExch(&status[0], PDN_ECUDA);
-            ok = false;
-            break;
-        }
-    }
-    atomicAdd(spent, (unsigned long long)(clock64() - t0));
-    return ok;
-}
-
 // ---- halo ------------------------------------------------------------------------------------------
 // vec_off: word offset of the vector inside every arena.  send_idx holds, peer after peer, the global
 // indices this rank owns and peer k reads (send_off / send_cnt per peer).
-struct HaloSend {
-    int32_t off[PEER_MAX], cnt[PEER_MAX], recv_cnt[PEER_MAX];
-};
 __global__ void __launch_bounds__(256) halo_push_kernel(PeerLink L, HaloSend h, size_t vec_off,
                                                         const int32_t *__restrict__ send_idx, unsigned int *ticket) {
     const unsigned long long *mine = L.arena[L.me] + vec_off;

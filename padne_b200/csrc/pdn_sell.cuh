@@ -83,11 +83,54 @@ struct SellOp {
 // DIST = false: the last CTA to finish runs the scalar recurrence (single GPU).
 // DIST = true : the last CTA stores this rank's three partial sums to sc->part[] and the recurrence
 //               runs in scalar_kernel after the all-reduce (pdn_multi.cuh).
+// What the last CTA does with the grid totals of the fused dot products (thread 0 holds acc):
+//   one GPU:                 the scalar recurrence (spmv_finalize)
+//   several, peer memory:    warp 0 all-reduces them over the ranks in place (pdn_peer_prim.cuh), then the recurrence
+//   several, NCCL fallback:  parked in sc->part for the all-reduce + scalar_kernel that follow
+template <int MODE, bool DIST>
+__device__ __forceinline__ void dots_tail(double (&acc)[3], Scal *sc, const PeerLink &L) {
+    if (DIST && L.world > 1) {
+        if (threadIdx.x >= 32) return;
+        const bool ok = peer_allreduce3(L, acc);
+        if (threadIdx.x != 0) return;
+        if (!ok) { sc->done = 3; sc->breakdown = 1; return; }
+        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
+        spmv_finalize<MODE>(acc, sc);
+        return;
+    }
+    if (threadIdx.x != 0) return;
+    if (DIST) {
+        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
+    } else {
+        spmv_finalize<MODE>(acc, sc);
+    }
+}
+
+// Override rows (constraint terminals): a terminal row sums the rows of every vertex its pad covers and can
+// hold thousands of entries, so one WARP per row (lanes stride over the entries, fixed shuffle tree), the rows
+// dealt round-robin to all warps of the grid.  (One thread per row in CTA 0 left a 30-80 us tail on the rank
+// that owns the terminals.)
+template <int MODE>
+__device__ __forceinline__ void special_rows(const SellOp &A, const double *__restrict__ x, double *__restrict__ y,
+                                             const double *__restrict__ aux0, double (&acc)[3], int32_t gwarp,
+                                             int32_t n_gwarp) {
+    const int lane = threadIdx.x & 31;
+    for (int32_t t = gwarp; t < A.n_special; t += n_gwarp) {
+        const int32_t row = A.sp_row[t];
+        if (row < A.row_begin || row >= A.row_end) continue;
+        double s2 = 0.0;
+        for (int32_t q = A.sp_rp[t] + lane; q < A.sp_rp[t + 1]; q += 32) s2 = fma(A.sp_va[q], x[A.sp_ci[q]], s2);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        if (lane == 0) row_epilogue<MODE>(row, s2, MODE == CG ? x[row] : 0.0, MODE != PLAIN ? aux0[row] : 0.0, y, acc);
+    }
+}
+
 template <int MODE, bool DIST>
 __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(SellOp A, const double *__restrict__ x,
                                                                double *__restrict__ y,
                                                                const double *__restrict__ aux0, Scal *sc,
-                                                               double *partials) {
+                                                               double *partials, PeerLink L) {
     __shared__ double red[3][SELL_WARPS];
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
@@ -157,24 +200,11 @@ __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(Sell
         if (live) row_epilogue<MODE>(row, sum, xi, ai, y, acc);
         s = sn; off = n_off; off1 = n_off1; mask = n_mask;
     }
-    // override rows (constraint terminals): CTA 0, one thread per row
-    if (blockIdx.x == 0) {
-        for (int32_t t = threadIdx.x; t < A.n_special; t += SELL_BLK) {
-            const int32_t row = A.sp_row[t];
-            if (row < A.row_begin || row >= A.row_end) continue;
-            double s2 = 0.0;
-            for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) s2 += A.sp_va[q] * x[A.sp_ci[q]];
-            row_epilogue<MODE>(row, s2, MODE == CG ? x[row] : 0.0, MODE != PLAIN ? aux0[row] : 0.0, y, acc);
-        }
-    }
+    special_rows<MODE>(A, x, y, aux0, acc, (int32_t)((blockIdx.x * SELL_BLK + threadIdx.x) >> 5),
+                       (int32_t)((gridDim.x * SELL_BLK) >> 5));
     if (MODE == PLAIN) return;
     if (!grid_reduce<3, SELL_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-    if (threadIdx.x != 0) return;
-    if (DIST) {
-        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
-    } else {
-        spmv_finalize<MODE>(acc, sc);
-    }
+    dots_tail<MODE, DIST>(acc, sc, L);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -223,7 +253,7 @@ template <int MODE, bool DIST>
 __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp A, const double *__restrict__ x,
                                                                      double *__restrict__ y,
                                                                      const double *__restrict__ aux0, Scal *sc,
-                                                                     double *partials) {
+                                                                     double *partials, PeerLink L) {
     extern __shared__ __align__(128) unsigned char st_smem[];
     pdl_trigger();
     pdl_wait();
@@ -346,24 +376,11 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         }
     }
     __syncthreads();
-    // override rows (constraint terminals): CTA 0, one thread per row
-    if (blockIdx.x == 0) {
-        for (int32_t t = threadIdx.x; t < A.n_special; t += ST_BLK) {
-            const int32_t row = A.sp_row[t];
-            if (row < A.row_begin || row >= A.row_end) continue;
-            double s2 = 0.0;
-            for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) s2 += A.sp_va[q] * x[A.sp_ci[q]];
-            row_epilogue<MODE>(row, s2, MODE == CG ? x[row] : 0.0, MODE != PLAIN ? aux0[row] : 0.0, y, acc);
-        }
-    }
+    special_rows<MODE>(A, x, y, aux0, acc, (int32_t)((blockIdx.x * ST_BLK + threadIdx.x) >> 5),
+                       (int32_t)((gridDim.x * ST_BLK) >> 5));
     if (MODE == PLAIN) return;
     if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-    if (threadIdx.x != 0) return;
-    if (DIST) {
-        sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
-    } else {
-        spmv_finalize<MODE>(acc, sc);
-    }
+    dots_tail<MODE, DIST>(acc, sc, L);
 }
 
 // ------------------------------------------------------------------------------------------------

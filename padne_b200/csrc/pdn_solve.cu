@@ -139,6 +139,7 @@ struct HaloPlan {
     std::vector<int64_t> begin;                 // [world+1] first owned row of every rank
     std::vector<int32_t> send_off, send_cnt, recv_off, recv_cnt;   // [world]
     int32_t n_send = 0, n_recv = 0;
+    int32_t n_interface = 0;                    // rows read by another rank, over ALL ranks (identical everywhere)
     DevBuf<int32_t> send_idx, recv_idx;
     DevBuf<double> sendbuf, recvbuf;
     HaloSend peer{};                            // the same plan for the peer-memory path (pdn_peer.cuh)
@@ -238,6 +239,13 @@ static void launch_spmv(pdn_ctx *ctx, const Operator &A, const double *x, double
 
 static bool is_dist(const pdn_ctx *ctx) { return pdn_comm_world(ctx) > 1; }
 
+// the peer-memory link of this rank, or an empty one (world = 0: single GPU / NCCL fallback)
+static PeerLink peer_link_or_none(pdn_ctx *ctx) {
+    if (is_dist(ctx) && pdn_peer_enabled(ctx)) return pdn_peer_link(ctx);
+    PeerLink none{};
+    return none;
+}
+
 template <int MODE, bool DIST>
 static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
     const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
@@ -251,7 +259,7 @@ static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, doub
     }
     int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
     grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + ST_WARPS - 1) / ST_WARPS));
-    PDN_LAUNCH_PDL(ctx, w->pdl, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p);
+    PDN_LAUNCH_PDL(ctx, w->pdl, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p, peer_link_or_none(ctx));
 #else
     auto kern = sell_spmv_kernel<MODE, DIST>;
     static int per_sm = 0;
@@ -261,7 +269,7 @@ static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, doub
     }
     int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
     grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + SELL_WARPS - 1) / SELL_WARPS));
-    PDN_LAUNCH(ctx, kern, (int)grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p);
+    PDN_LAUNCH(ctx, kern, (int)grid, SELL_BLK, 0, w->A, x, y, aux, w->d_sc, w->partials.p, peer_link_or_none(ctx));
 #endif
 }
 
@@ -274,7 +282,8 @@ template <int MODE>
 static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
     if (is_dist(ctx)) {
         launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
-        if (MODE != PLAIN) dist_reduce<MODE>(ctx, w);
+        // peer memory: the kernel's last CTA has all-reduced the dots and run the recurrence itself
+        if (MODE != PLAIN && !pdn_peer_enabled(ctx)) dist_reduce<MODE>(ctx, w);
     } else {
         launch_sell_kernel<MODE, false>(ctx, w, x, y, aux);
     }
@@ -290,16 +299,8 @@ __global__ void __launch_bounds__(256) halo_unpack_kernel(int32_t k, const int32
     for (int32_t i = blockIdx.x * 256 + threadIdx.x; i < k; i += gridDim.x * 256) vec[idx[i]] = buf[i];
 }
 
-// PADNE_B200_DIST_SKIP=halo,dots,rc leaves an exchange out of the iteration (profiles/dist_probe.py: what does
-// each one cost?).  The numbers a solve returns with it are garbage by construction.
-static bool dist_skip(const char *what) {
-    const char *e = getenv("PADNE_B200_DIST_SKIP");
-    return e && strstr(e, what) != nullptr;
-}
-
 static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
     if (!is_dist(ctx)) return;
-    if (dist_skip("halo")) return;
     HaloPlan &h = w->halo;
     if (h.n_send == 0 && h.n_recv == 0) return;
     if (pdn_peer_enabled(ctx)) {
@@ -326,10 +327,6 @@ static void halo_exchange(pdn_ctx *ctx, SolveWork *w, double *vec) {
 // sum sc->part[0..2] over the ranks and run recurrence WHICH (scalar_kernel numbering)
 template <int WHICH>
 static void dist_reduce(pdn_ctx *ctx, SolveWork *w) {
-    if (dist_skip("dots")) {
-        PDN_LAUNCH(ctx, scalar_kernel<WHICH>, 1, 1, 0, w->d_sc, w->d_out);
-        return;
-    }
     if (pdn_peer_enabled(ctx)) {
         PDN_LAUNCH(ctx, peer_reduce_kernel<WHICH>, 1, 32, 0, pdn_peer_link(ctx), w->d_sc, w->d_out);
     } else {
@@ -573,24 +570,55 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w) {
 // two-level: x_c = A_c^-1 r_c, z = D^-1 r + P x_c  (r_c was accumulated by the update / init kernel)
 // slot: which half of rc_fix holds the restriction (-1: iteration parity, PCG); src / dst: the vector that
 // was restricted and the preconditioned one
+// true when coarse_z_kernel also performs the halo exchange of the vector it writes: peer memory and an
+// interface small enough for one CTA to push (a via-heavy board keeps the multi-CTA push kernel)
+static bool halo_in_coarse_z(pdn_ctx *ctx, SolveWork *w) {
+    const char *e = getenv("PADNE_B200_HALO_FUSED");   // 0: keep the separate push / wait kernels (same on every rank)
+    if (e && e[0] == '0') return false;
+    return w->two_level && is_dist(ctx) && pdn_peer_enabled(ctx) && w->halo.n_interface <= 32768;
+}
+
 void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, double boost, const double *src,
-                               double *dst) {
-    if (is_dist(ctx) && !dist_skip("rc")) {   // every rank restricted its own rows: exact integer sum, identical everywhere
-        if (pdn_peer_enabled(ctx))
+                               double *dst, bool rc_summed = false) {
+    // several GPUs: every rank restricted its own rows -> exact integer sum, identical everywhere.  NCCL
+    // fallback: both slots (the idle one is all zeros).  Peer memory: cg_update_tl_kernel's last CTA has already
+    // done it (rc_summed); the other restricting kernels are followed by the exchange kernel.
+    if (is_dist(ctx)) {
+        if (!pdn_peer_enabled(ctx)) pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
+        else if (!rc_summed)
             PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, slot);
-        else   // both slots are reduced (2 nc values): the idle one is all zeros
-            pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
     }
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
     PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_fix.p, w->xc.p, slot,
                    boost);
-    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_z_kernel, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src,
-                   w->agg.p, w->xc.p, dst);
+    PeerLink L{};
+    HaloSend hs{};
+    size_t vec_off = 0;
+    unsigned int *ticket = nullptr;
+    if (halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0)) {
+        int which = -1;
+        for (int v = 0; v < PDN_PA_NVEC; v++)
+            if (dst == pdn_peer_vec(ctx, v)) which = v;
+        if (which < 0) PDN_FAIL(PDN_ECUDA, "coarse correction: the vector is not inside the peer arena");
+        L = pdn_peer_link(ctx);
+        hs = w->halo.peer;
+        vec_off = pdn_peer_vec_offset(ctx, which);
+        ticket = pdn_peer_ticket(ctx);
+    }
+    if (L.world > 1) {
+        const int64_t npair = (w->row_end - w->row_begin + 1) / 2;
+        const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * 2, (npair + 1023) / 1024));
+        PDN_LAUNCH(ctx, coarse_z_kernel<1024>, zgrid, 1024, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src, w->agg.p,
+                   w->xc.p, dst, L, hs, vec_off, w->halo.send_idx.p, ticket);
+    } else {
+        PDN_LAUNCH_PDL(ctx, w->pdl, coarse_z_kernel<CO_BLK>, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p,
+                       src, w->agg.p, w->xc.p, dst, L, hs, vec_off, w->halo.send_idx.p, ticket);
+    }
 }
 
 void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     const int64_t r0 = w->row_begin, r1 = w->row_end;
-    halo_exchange(ctx, w, w->z.p);
+    if (!halo_in_coarse_z(ctx, w)) halo_exchange(ctx, w, w->z.p);
     launch_sell<CG>(ctx, w, w->z.p, w->w.p, w->r.p);
     if (w->two_level) {
         const int64_t npair = (r1 - r0 + 1) / 2;
@@ -601,8 +629,8 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         }
         const int tgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * tl_per_sm, (npair + TLB - 1) / TLB));
         PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_tl_kernel, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
-                       w->r.p, w->agg.p, w->rc_fix.p, w->nc);
-        enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p);
+                       w->r.p, w->agg.p, w->rc_fix.p, w->nc, peer_link_or_none(ctx), &w->d_sc->ticket[3]);
+        enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, /*rc_summed=*/pdn_peer_enabled(ctx));
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                    w->x.p, w->r.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
@@ -614,7 +642,7 @@ void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     const bool dist = is_dist(ctx);
     const int32_t *no_agg = nullptr;
     long long *no_rc = nullptr;
-    halo_exchange(ctx, w, w->ph.p);
+    if (!halo_in_coarse_z(ctx, w)) halo_exchange(ctx, w, w->ph.p);
     launch_sell<BICG_V>(ctx, w, w->ph.p, w->vv.p, w->rhat.p);
     if (w->two_level) {
         PDN_LAUNCH(ctx, bicg_s_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->s.p, w->sh.p,
@@ -624,7 +652,7 @@ void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         PDN_LAUNCH(ctx, bicg_s_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->vv.p, w->s.p, w->sh.p,
                    no_agg, no_rc, 0);
     }
-    halo_exchange(ctx, w, w->sh.p);
+    if (!halo_in_coarse_z(ctx, w)) halo_exchange(ctx, w, w->sh.p);
     launch_sell<BICG_T>(ctx, w, w->sh.p, w->tt.p, w->s.p);
     if (dist) {
         PDN_LAUNCH(ctx, bicg_x_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->ph.p, w->sh.p, w->s.p, w->tt.p,
@@ -696,6 +724,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     // one CUDA graph = check_every iterations; kernels turn into no-ops once sc->done is set
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
+    int per_iter = 0;
     auto build_graph = [&]() {
         const int64_t launches_before = ctx->launches;
         // PCG on one GPU: the four kernels of an iteration are chained by programmatic dependent launches
@@ -717,10 +746,9 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         w->pdl = false;
         PDN_CUDA(cudaStreamEndCapture(st, &graph));
         PDN_CUDA(cudaGraphInstantiate(&exec, graph, 0));
+        per_iter = (int)((ctx->launches - launches_before) / check_every);   // kernels of one captured iteration
         ctx->launches = launches_before;  // capture is not execution
     };
-    const int per_iter = (method == PDN_METHOD_PCG ? 2 : 5) + (dist ? (method == PDN_METHOD_PCG ? 3 : 7) : 0) +
-                         (w->two_level ? (method == PDN_METHOD_PCG ? 2 : 4) + (dist ? (method == PDN_METHOD_PCG ? 1 : 2) : 0) : 0);
     build_graph();
 
     auto cleanup = [&]() {
@@ -754,6 +782,19 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                            w->partials.p, agg, rc, w->nc);
                 if (dist) dist_reduce<6>(ctx, w);
                 if (tl) enqueue_coarse_correction(ctx, w, vgrid, 1, BICG_BOOST, w->p.p, w->ph.p);
+            }
+            if (attempt == 0 && getenv("PADNE_B200_KTIME")) {
+                KernelTimes kt;
+                ctx->ktime = &kt;
+                kt.active = true;
+                kt.mark("start", st);
+                for (int k = 0; k < check_every; k++) {
+                    if (method == PDN_METHOD_PCG) enqueue_pcg_iteration(ctx, w, vgrid);
+                    else enqueue_bicg_iteration(ctx, w, vgrid);
+                }
+                kt.active = false;
+                ctx->ktime = nullptr;
+                kt.report(pdn_comm_rank(ctx));
             }
             while (true) {
                 PDN_CUDA(cudaGraphLaunch(exec, st));
@@ -903,6 +944,13 @@ __global__ void __launch_bounds__(256) halo_scatter_kernel(int list, RowPart par
         if (halo_item(list, part, me, v, needmask, c)) out[offs[v]] = c;
     }
 }
+// number of rows some other rank reads (the same on every rank: the marks are replicated)
+__global__ void __launch_bounds__(256) halo_count_kernel(int64_t n, const uint32_t *__restrict__ needmask, int32_t *count) {
+    int32_t c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) c += needmask[i] != 0u;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
 // first list position of every peer: out[k] (send), out[world + 1 + k] (recv), k = 0 .. world
 __global__ void halo_offsets_kernel(RowPart part, int me, const int32_t *__restrict__ offs_send,
                                     const int32_t *__restrict__ offs_recv, int32_t *__restrict__ out) {
@@ -930,8 +978,10 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     w->tmp_i32b.reserve((size_t)n_items + 1);       // flags
     w->halo_col.reserve((size_t)n_send_items + 1);  // offsets of the send items
     w->halo_mask.reserve((size_t)n_recv_items + 1); // offsets of the receive items
-    w->tmp_i32a.reserve((size_t)2 * (world + 1));
-    std::vector<int32_t> offs((size_t)2 * (world + 1), 0);
+    w->tmp_i32a.reserve((size_t)2 * (world + 1) + 1);
+    std::vector<int32_t> offs((size_t)2 * (world + 1) + 1, 0);
+    PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p + 2 * (world + 1), 0, sizeof(int32_t), st));
+    PDN_LAUNCH(ctx, halo_count_kernel, pdn_grid(ctx, n, 256, 8), 256, 0, n, w->needmask.p, w->tmp_i32a.p + 2 * (world + 1));
     if (n_send_items > 0) {
         PDN_LAUNCH(ctx, halo_flag_kernel, pdn_grid(ctx, n_send_items, 256, 8), 256, 0, 0, part, me, n_send_items,
                    w->needmask.p, w->tmp_i32b.p);
@@ -955,6 +1005,7 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     }
     h.n_send = offs[world];
     h.n_recv = offs[2 * world + 1];
+    h.n_interface = offs[2 * (world + 1)];
     h.peer = HaloSend{};
     for (int k = 0; k < world && k < PEER_MAX; k++) {
         h.peer.off[k] = h.send_off[k];
@@ -1106,6 +1157,29 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     return true;
 }
 
+void KernelTimes::report(int rank) {
+    if (marks.size() < 2) return;
+    cudaEventSynchronize(marks.back().second);
+    std::map<std::string, std::pair<double, int>> agg;
+    for (size_t i = 1; i < marks.size(); i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second);
+        auto &a = agg[marks[i].first];
+        a.first += ms;
+        a.second++;
+    }
+    std::string out;
+    char buf[160];
+    for (auto &kv : agg) {
+        snprintf(buf, sizeof buf, "  %-44s n=%4d  mean %.1f us\n", kv.first.c_str(), kv.second.second,
+                 1e3 * kv.second.first / kv.second.second);
+        out += buf;
+    }
+    fprintf(stderr, "[padne_b200 ktime rank %d] event-to-event, eager launches:\n%s", rank, out.c_str());
+    for (auto &m : marks) cudaEventDestroy(m.second);
+    marks.clear();
+}
+
 // PADNE_B200_TRACE=1: wall-clock per phase of one solve (each mark drains the stream, so the phases add
 // up to more than an untraced solve); printed to stderr by every rank
 struct PhaseTrace {
@@ -1125,6 +1199,12 @@ struct PhaseTrace {
         snprintf(buf, sizeof buf, " %s=%.3f", name, std::chrono::duration<double, std::milli>(t1 - t0).count());
         out += buf;
         t0 = t1;
+    }
+    void note(const char *name, long long v) {
+        if (!on) return;
+        char buf[96];
+        snprintf(buf, sizeof buf, " %s=%lld", name, v);
+        out += buf;
     }
     ~PhaseTrace() {
         if (on) fprintf(stderr, "[padne_b200 trace rank %d]%s (ms)\n", rank, out.c_str());
@@ -1393,6 +1473,8 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     w->A.sp_ci = w->sp_ci.p;
     w->A.sp_va = w->sp_va.p;
     trace.mark("override_rows");
+    trace.note("n_special", (long long)nT);
+    trace.note("special_nnz", (long long)r_ci.size());
     // rows of the Krylov loop this rank owns: whole sort windows, split evenly
     {
         const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
