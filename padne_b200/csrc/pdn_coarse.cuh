@@ -376,12 +376,13 @@ template <int BLK>
 __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                        const double *__restrict__ dinv, const double *__restrict__ r,
                                                        const int32_t *__restrict__ agg, const double *__restrict__ xc,
-                                                       double *__restrict__ z, PeerLink L, HaloSend hs, size_t vec_off,
-                                                       const int32_t *__restrict__ send_idx, unsigned int *ticket) {
+                                                       double *__restrict__ z, const PeerLink *Lp, const HaloSend *hsp,
+                                                       size_t vec_off, const int32_t *__restrict__ send_idx,
+                                                       unsigned int *ticket) {
     pdl_trigger();
     pdl_wait();
     if (sc->done) return;
-    if (L.world > 1 && blockIdx.x == 0 && threadIdx.x == 0) peer_log(L, 7);
+    if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 7);
     const int64_t npair = (n - r0 + 1) >> 1;
     for (int64_t t = (int64_t)blockIdx.x * BLK + threadIdx.x; t < npair; t += (int64_t)gridDim.x * BLK) {
         const int64_t i = r0 + 2 * t;
@@ -396,7 +397,7 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
             z[i] = dinv[i] * r[i] + (a >= 0 ? __ldg(&xc[a]) : 0.0);
         }
     }
-    if (L.world <= 1) return;
+    if (BLK != 1024 || Lp == nullptr) return;    // the tail only exists in the multi-GPU instantiation
     __shared__ bool is_last;
     __threadfence();
     __syncthreads();
@@ -405,6 +406,8 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
     if (!is_last) return;
     if (threadIdx.x == 0) *ticket = 0u;
     __threadfence();
+    const PeerLink &L = *Lp;
+    const HaloSend &hs = *hsp;
     const unsigned long long *mine = L.arena[L.me] + vec_off;
     for (int k = 0; k < L.world; k++) {
         if (k == L.me || hs.cnt[k] == 0) continue;

@@ -269,6 +269,9 @@ bool pdn_peer_enabled(const pdn_ctx *ctx);
 // collective: (re)allocate the arena for vectors of n_cap doubles and map every peer's
 void pdn_peer_ensure(pdn_ctx *ctx, int64_t n_cap);
 PdnPeerLink pdn_peer_link(const pdn_ctx *ctx);
+// the same in device memory (valid after pdn_peer_ensure): hot kernels take this pointer, a by-value struct
+// indexed by rank would be copied to local memory by every thread
+const PdnPeerLink *pdn_peer_link_dev(const pdn_ctx *ctx);
 double *pdn_peer_vec(const pdn_ctx *ctx, int which);   // vector `which` (0..3) inside the local arena
 size_t pdn_peer_vec_offset(const pdn_ctx *ctx, int which);   // its word offset inside every arena
 unsigned int *pdn_peer_ticket(const pdn_ctx *ctx);

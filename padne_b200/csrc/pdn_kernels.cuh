@@ -229,13 +229,13 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
                                                               double *__restrict__ p, double *__restrict__ s,
                                                               double *__restrict__ x, double *__restrict__ r,
                                                               const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc,
-                                                              PeerLink L, unsigned int *ticket) {
+                                                              const PeerLink *Lp, unsigned int *ticket) {
     __shared__ long long tab[CO_MAX];
     pdl_trigger();
     for (int a = threadIdx.x; a < nc; a += TLB) tab[a] = 0;
     pdl_wait();
     if (sc->done) return;
-    if (L.world > 1 && blockIdx.x == 0 && threadIdx.x == 0) peer_log(L, 6);
+    if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 6);
     const double alpha = sc->alpha, beta = sc->beta;
     const double fix = CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300));
     unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc;
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
         const long long v = tab[a];
         if (v != 0) atomicAdd(&rc[a], (unsigned long long)v);
     }
-    if (L.world <= 1) return;
+    if (Lp == nullptr) return;
     // several GPUs: the last CTA to finish sums r_c over the ranks (peer-memory stores, pdn_peer_prim.cuh)
     __shared__ bool is_last;
     __threadfence();
@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
     if (!is_last) return;
     if (threadIdx.x == 0) *ticket = 0u;
     __threadfence();
-    peer_sum_i64_cta(L, reinterpret_cast<long long *>(rc), nc);
+    peer_sum_i64_cta(*Lp, reinterpret_cast<long long *>(rc), nc);
 }
 
 // start / restart from the residual r:  z = dinv r (or its restriction, TL);  p = s = 0

@@ -85,7 +85,8 @@ struct PdnComm {
     unsigned long long *arena = nullptr;              // local
     unsigned long long *peer[PDN_PEER_MAX] = {};      // peer[k] = rank k's arena mapped here (peer[rank] = arena)
     int64_t n_cap = 0;                                // doubles per exchanged vector
-    unsigned long long *epoch = nullptr;              // device [4]
+    unsigned long long *epoch = nullptr;              // device [8 + log]
+    PdnPeerLink *link_d = nullptr;                    // device copy of pdn_peer_link() (kernels take a pointer)
     unsigned int *ticket = nullptr;                   // device [4]
 };
 
@@ -131,7 +132,11 @@ void pdn_peer_ensure(pdn_ctx *ctx, int64_t n) {
         c->peer[k] = (unsigned long long *)ptr;
     }
     c->n_cap = n_cap;
+    if (!c->link_d) PDN_CUDA(cudaMalloc((void **)&c->link_d, sizeof(PdnPeerLink)));
+    const PdnPeerLink L = pdn_peer_link(ctx);
+    PDN_CUDA(cudaMemcpy(c->link_d, &L, sizeof L, cudaMemcpyHostToDevice));
 }
+const PdnPeerLink *pdn_peer_link_dev(const pdn_ctx *ctx) { return ctx->comm ? ctx->comm->link_d : nullptr; }
 
 PdnPeerLink pdn_peer_link(const pdn_ctx *ctx) {
     PdnPeerLink L{};
@@ -185,6 +190,7 @@ void pdn_comm_release(pdn_ctx *ctx) {
         }
         peer_unmap(ctx->comm);
         if (ctx->comm->epoch) cudaFree(ctx->comm->epoch);
+        if (ctx->comm->link_d) cudaFree(ctx->comm->link_d);
         if (ctx->comm->ticket) cudaFree(ctx->comm->ticket);
         if (ctx->comm->comm) nccl().CommDestroy(ctx->comm->comm);
         delete ctx->comm;

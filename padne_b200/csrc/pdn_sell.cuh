@@ -88,10 +88,10 @@ struct SellOp {
 //   several, peer memory:    warp 0 all-reduces them over the ranks in place (pdn_peer_prim.cuh), then the recurrence
 //   several, NCCL fallback:  parked in sc->part for the all-reduce + scalar_kernel that follow
 template <int MODE, bool DIST>
-__device__ __forceinline__ void dots_tail(double (&acc)[3], Scal *sc, const PeerLink &L) {
-    if (DIST && L.world > 1) {
+__device__ __forceinline__ void dots_tail(double (&acc)[3], Scal *sc, const PeerLink *Lp) {
+    if (DIST && Lp != nullptr) {
         if (threadIdx.x >= 32) return;
-        const bool ok = peer_allreduce3(L, acc);
+        const bool ok = peer_allreduce3(*Lp, acc);
         if (threadIdx.x != 0) return;
         if (!ok) { sc->done = 3; sc->breakdown = 1; return; }
         sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
@@ -130,7 +130,7 @@ template <int MODE, bool DIST>
 __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(SellOp A, const double *__restrict__ x,
                                                                double *__restrict__ y,
                                                                const double *__restrict__ aux0, Scal *sc,
-                                                               double *partials, PeerLink L) {
+                                                               double *partials, const PeerLink *Lp) {
     __shared__ double red[3][SELL_WARPS];
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(Sell
                        (int32_t)((gridDim.x * SELL_BLK) >> 5));
     if (MODE == PLAIN) return;
     if (!grid_reduce<3, SELL_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-    dots_tail<MODE, DIST>(acc, sc, L);
+    dots_tail<MODE, DIST>(acc, sc, Lp);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -253,7 +253,7 @@ template <int MODE, bool DIST>
 __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp A, const double *__restrict__ x,
                                                                      double *__restrict__ y,
                                                                      const double *__restrict__ aux0, Scal *sc,
-                                                                     double *partials, PeerLink L) {
+                                                                     double *partials, const PeerLink *Lp) {
     extern __shared__ __align__(128) unsigned char st_smem[];
     pdl_trigger();
     pdl_wait();
@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
                        (int32_t)((gridDim.x * ST_BLK) >> 5));
     if (MODE == PLAIN) return;
     if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-    dots_tail<MODE, DIST>(acc, sc, L);
+    dots_tail<MODE, DIST>(acc, sc, Lp);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -143,6 +143,7 @@ struct HaloPlan {
     DevBuf<int32_t> send_idx, recv_idx;
     DevBuf<double> sendbuf, recvbuf;
     HaloSend peer{};                            // the same plan for the peer-memory path (pdn_peer.cuh)
+    DevBuf<HaloSend> peer_d;                    // ... in device memory (coarse_z_kernel's tail)
 };
 
 struct SolveWork {
@@ -239,11 +240,10 @@ static void launch_spmv(pdn_ctx *ctx, const Operator &A, const double *x, double
 
 static bool is_dist(const pdn_ctx *ctx) { return pdn_comm_world(ctx) > 1; }
 
-// the peer-memory link of this rank, or an empty one (world = 0: single GPU / NCCL fallback)
-static PeerLink peer_link_or_none(pdn_ctx *ctx) {
-    if (is_dist(ctx) && pdn_peer_enabled(ctx)) return pdn_peer_link(ctx);
-    PeerLink none{};
-    return none;
+// the peer-memory link of this rank in device memory, or null (single GPU / NCCL fallback)
+static const PeerLink *peer_link_or_none(pdn_ctx *ctx) {
+    if (is_dist(ctx) && pdn_peer_enabled(ctx)) return pdn_peer_link_dev(ctx);
+    return nullptr;
 }
 
 template <int MODE, bool DIST>
@@ -591,8 +591,7 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
     PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_fix.p, w->xc.p, slot,
                    boost);
-    PeerLink L{};
-    HaloSend hs{};
+    const PeerLink *Lp = nullptr;
     size_t vec_off = 0;
     unsigned int *ticket = nullptr;
     if (halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0)) {
@@ -600,19 +599,18 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
         for (int v = 0; v < PDN_PA_NVEC; v++)
             if (dst == pdn_peer_vec(ctx, v)) which = v;
         if (which < 0) PDN_FAIL(PDN_ECUDA, "coarse correction: the vector is not inside the peer arena");
-        L = pdn_peer_link(ctx);
-        hs = w->halo.peer;
+        Lp = pdn_peer_link_dev(ctx);
         vec_off = pdn_peer_vec_offset(ctx, which);
         ticket = pdn_peer_ticket(ctx);
     }
-    if (L.world > 1) {
+    if (Lp != nullptr) {
         const int64_t npair = (w->row_end - w->row_begin + 1) / 2;
-        const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * 2, (npair + 1023) / 1024));
+        const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));   // one CTA per SM (60 registers)
         PDN_LAUNCH(ctx, coarse_z_kernel<1024>, zgrid, 1024, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src, w->agg.p,
-                   w->xc.p, dst, L, hs, vec_off, w->halo.send_idx.p, ticket);
+                   w->xc.p, dst, Lp, w->halo.peer_d.p, vec_off, w->halo.send_idx.p, ticket);
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, coarse_z_kernel<CO_BLK>, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p,
-                       src, w->agg.p, w->xc.p, dst, L, hs, vec_off, w->halo.send_idx.p, ticket);
+                       src, w->agg.p, w->xc.p, dst, Lp, (const HaloSend *)nullptr, vec_off, w->halo.send_idx.p, ticket);
     }
 }
 
@@ -1014,6 +1012,9 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     }
     h.send_idx.reserve((size_t)h.n_send + 1);
     h.recv_idx.reserve((size_t)h.n_recv + 1);
+    h.peer_d.reserve(1);
+    PDN_CUDA(cudaMemcpyAsync(h.peer_d.p, &h.peer, sizeof(HaloSend), cudaMemcpyHostToDevice, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
     if (h.n_send > 0)
         PDN_LAUNCH(ctx, halo_scatter_kernel, pdn_grid(ctx, n_send_items, 256, 8), 256, 0, 0, part, me, n_send_items,
                    w->needmask.p, w->halo_col.p, h.send_idx.p);
