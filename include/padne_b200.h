@@ -175,6 +175,17 @@ int pdn_comm_info(pdn_ctx *ctx, int *rank, int *world);
 int pdn_power_density(pdn_ctx *ctx, int64_t n_v, const double *xy, const double *val, int64_t n_t,
                       const int32_t *tri, double conductivity, double *p /*[n_t]*/, int on_device);
 
+/* ---- next row F3: nearest mesh vertex of every connection point ------------------------------------
+ * Replaces the per-layer scipy KDTree of NodeIndexer (padne/solver.py:356-396 builds it, :421-433 queries
+ * it once per Connection): out_index[q] = global index (VertexIndexer order, padne/solver.py:216-229) of the
+ * vertex nearest to q_xy[q] among ALL meshes m with mesh_layer[m] == q_layer[q]; -1 when the layer has no
+ * vertex.  Squared Euclidean distance dx*dx + dy*dy in binary64, the lowest index wins an exact tie
+ * (a KD-tree's tie order is unspecified).  out_d2 (squared distances) may be NULL. */
+int pdn_nearest_vertex(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off /*[n_mesh+1]*/,
+                       const int32_t *mesh_layer /*[n_mesh]*/, const double *xy /*[n_v,2]*/, int64_t n_q,
+                       const double *q_xy /*[n_q,2]*/, const int32_t *q_layer /*[n_q]*/,
+                       int64_t *out_index /*[n_q]*/, double *out_d2 /*[n_q] or NULL*/, int on_device);
+
 #ifdef __cplusplus
 }
 #endif

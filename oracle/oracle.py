@@ -131,3 +131,33 @@ def assemble_and_solve(fs, stamps_and_rhs):
     indptr, indices, data = assemble(fs, stamps_and_rhs[:4])
     v, res, ig = solve(indptr, indices, data, stamps_and_rhs[4])
     return (indptr, indices, data), v, res, ig
+
+
+def nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer):
+    """Row F3: what ``NodeIndexer.create`` gets from its per-layer KD-trees (``padne/solver.py:356-396``
+    build, ``:421-433`` query), restated as a brute-force search in numpy: per query the vertex with the
+    smallest ``dx*dx + dy*dy`` among all meshes of the query's layer, lowest global index on an exact
+    tie, -1 when the layer has no vertex.  ``tests/test_oracle.py`` pins it against
+    ``scipy.spatial.KDTree(..., leafsize=32).query`` -- the reference's own call -- on tie-free inputs.
+    Returns (index int64 [n_q], squared distance [n_q])."""
+    v_off = np.asarray(v_off, np.int64)
+    mesh_layer = np.asarray(mesh_layer, np.int32)
+    xy = np.asarray(xy, np.float64).reshape(-1, 2)
+    q_xy = np.asarray(q_xy, np.float64).reshape(-1, 2)
+    q_layer = np.asarray(q_layer, np.int32)
+    v_layer = np.repeat(mesh_layer, np.diff(v_off))
+    out = np.full(q_xy.shape[0], -1, np.int64)
+    d2 = np.full(q_xy.shape[0], np.inf)
+    for layer in np.unique(q_layer):
+        idx = np.flatnonzero(v_layer == layer)
+        if idx.size == 0:
+            continue
+        p = xy[idx]
+        for q in np.flatnonzero(q_layer == layer):
+            dx = p[:, 0] - q_xy[q, 0]
+            dy = p[:, 1] - q_xy[q, 1]
+            d = dx * dx + dy * dy
+            k = int(np.argmin(d))            # first minimum == lowest global index (idx is ascending)
+            out[q] = idx[k]
+            d2[q] = d[k]
+    return out, d2

@@ -27,7 +27,7 @@ METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 SYMBOLS = ("pdn_create", "pdn_destroy", "pdn_strerror", "pdn_last_error", "pdn_launch_count",
            "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_get_csr", "pdn_get_shape",
            "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density",
-           "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info")
+           "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info", "pdn_nearest_vertex")
 
 
 class SingularSystemError(RuntimeError):
@@ -102,6 +102,7 @@ def load_library(path: str | None = None):
     lib.pdn_spmv.argtypes = [P, P, P, ctypes.c_int]
     lib.pdn_bench_spmv.argtypes = [P, I32, ctypes.c_int, ctypes.POINTER(D)]
     lib.pdn_power_density.argtypes = [P, I64, P, P, I64, P, D, P, ctypes.c_int]
+    lib.pdn_nearest_vertex.argtypes = [P, I32, P, P, P, I64, P, P, P, P, ctypes.c_int]
     lib.pdn_comm_unique_id.argtypes = [P]
     lib.pdn_comm_init.argtypes = [P, ctypes.c_int, ctypes.c_int, P]
     lib.pdn_comm_destroy.argtypes = [P]
@@ -336,6 +337,28 @@ class Context:
         self._check(self._lib.pdn_power_density(self._ctx, xy.shape[0], _ptr(xy), _ptr(values), tri.shape[0],
                                                 _ptr(tri), float(conductivity), _ptr(p), 0), "power_density")
         return p
+
+
+    # -- row F3 ---------------------------------------------------------------------------------------
+    def nearest_vertex(self, v_off, mesh_layer, xy, q_xy, q_layer, return_d2: bool = False):
+        """Nearest vertex of every query point among the meshes of its layer: the ``KDTree.query`` loop of
+        ``NodeIndexer.create`` (``padne/solver.py:421-433``).  Returns global vertex indices (int64, -1 when
+        the layer is empty) and, optionally, the squared distances."""
+        v_off = _np(v_off, np.int64)
+        mesh_layer = _np(mesh_layer, np.int32)
+        xy = _np(xy, np.float64).reshape(-1, 2)
+        q_xy = _np(q_xy, np.float64).reshape(-1, 2)
+        q_layer = _np(q_layer, np.int32)
+        if v_off.shape[0] != mesh_layer.shape[0] + 1 or q_xy.shape[0] != q_layer.shape[0]:
+            raise ValueError("nearest_vertex: inconsistent array lengths")
+        if v_off[-1] != xy.shape[0]:
+            raise ValueError("nearest_vertex: v_off[-1] must equal the number of vertices")
+        out = np.empty(q_xy.shape[0], np.int64)
+        d2 = np.empty(q_xy.shape[0], np.float64) if return_d2 else None
+        self._check(self._lib.pdn_nearest_vertex(self._ctx, mesh_layer.shape[0], _ptr(v_off), _ptr(mesh_layer), _ptr(xy),
+                                                 q_xy.shape[0], _ptr(q_xy), _ptr(q_layer), _ptr(out),
+                                                 _ptr(d2) if return_d2 else None, 0), "nearest_vertex")
+        return (out, d2) if return_d2 else out
 
 
 _default_ctx: dict[int, Context] = {}

@@ -306,4 +306,19 @@ int pdn_power_density(pdn_ctx *ctx, int64_t n_v, const double *xy, const double 
     });
 }
 
+int pdn_nearest_vertex(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const int32_t *mesh_layer, const double *xy,
+                       int64_t n_q, const double *q_xy, const int32_t *q_layer, int64_t *out_index, double *out_d2,
+                       int on_device) {
+    return pdn_guard(ctx, [&] {
+        if (n_mesh < 0 || n_q < 0 || !v_off || (n_mesh > 0 && !mesh_layer) || (n_q > 0 && (!q_xy || !q_layer || !out_index)))
+            PDN_FAIL(PDN_EINVAL, "nearest_vertex: bad arguments");
+        if (!on_device) {
+            for (int32_t m = 0; m < n_mesh; m++)
+                if (v_off[m + 1] < v_off[m]) PDN_FAIL(PDN_EINVAL, "nearest_vertex: v_off must be non-decreasing");
+            if (n_mesh > 0 && v_off[n_mesh] > v_off[0] && !xy) PDN_FAIL(PDN_EINVAL, "nearest_vertex: xy is null");
+        }
+        pdn_nearest_vertex_impl(ctx, n_mesh, v_off, mesh_layer, xy, n_q, q_xy, q_layer, out_index, out_d2, on_device != 0);
+    });
+}
+
 }  // extern "C"

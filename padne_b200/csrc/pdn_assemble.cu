@@ -430,6 +430,113 @@ void pdn_power_density_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, const d
     raise_device_status(ctx, "power_density");
 }
 
+// ------------------------------------------------------------------------------------------------
+// next row F3: nearest mesh vertex of every connection point (NodeIndexer, padne/solver.py:356-396, 421-433).
+// The reference builds one scipy KDTree per layer over all vertices of all meshes of that layer and
+// queries it once per connection.  Here: a CTA takes NQ queries, walks the meshes whose layer matches and
+// keeps per-thread minima of the squared distance dx*dx + dy*dy (separately rounded: this unit is compiled
+// with -fmad=false), then reduces (distance, global index) with the LOWEST index winning a tie.  The
+// vertices are read once per NQ queries; everything is L2-resident at board sizes.
+// ------------------------------------------------------------------------------------------------
+constexpr int NQ = 8;
+__global__ void __launch_bounds__(256) nearest_vertex_kernel(int32_t n_mesh, const int64_t *__restrict__ v_off,
+                                                             const int32_t *__restrict__ mesh_layer,
+                                                             const double2 *__restrict__ xy, int64_t n_q,
+                                                             const double2 *__restrict__ q_xy,
+                                                             const int32_t *__restrict__ q_layer,
+                                                             int64_t *__restrict__ out_index, double *__restrict__ out_d2) {
+    __shared__ double s_d[NQ][8];
+    __shared__ long long s_i[NQ][8];
+    const int64_t q0 = (int64_t)blockIdx.x * NQ;
+    double qx[NQ], qy[NQ], best[NQ];
+    long long bi[NQ];
+    int32_t ql[NQ];
+#pragma unroll
+    for (int k = 0; k < NQ; k++) {
+        const bool live = q0 + k < n_q;
+        const double2 q = live ? q_xy[q0 + k] : make_double2(0.0, 0.0);
+        qx[k] = q.x; qy[k] = q.y;
+        ql[k] = live ? q_layer[q0 + k] : -2147483647;
+        best[k] = INFINITY;
+        bi[k] = -1;
+    }
+    for (int32_t m = 0; m < n_mesh; m++) {
+        const int32_t layer = mesh_layer[m];
+        unsigned mask = 0;
+#pragma unroll
+        for (int k = 0; k < NQ; k++) mask |= (ql[k] == layer ? 1u : 0u) << k;
+        if (!mask) continue;
+        for (int64_t i = v_off[m] + threadIdx.x; i < v_off[m + 1]; i += 256) {   // ascending index per thread
+            const double2 p = xy[i];
+#pragma unroll
+            for (int k = 0; k < NQ; k++) {
+                const double dx = p.x - qx[k], dy = p.y - qy[k];
+                const double d = dx * dx + dy * dy;
+                if (((mask >> k) & 1u) && d < best[k]) { best[k] = d; bi[k] = i; }
+            }
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NQ; k++) {
+        double d = best[k];
+        long long i = bi[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double d2 = __shfl_xor_sync(0xffffffffu, d, o);
+            const long long i2 = __shfl_xor_sync(0xffffffffu, i, o);
+            if (i2 >= 0 && (i < 0 || d2 < d || (d2 == d && i2 < i))) { d = d2; i = i2; }
+        }
+        if (lane == 0) { s_d[k][warp] = d; s_i[k][warp] = i; }
+    }
+    __syncthreads();
+    if (threadIdx.x < NQ && q0 + threadIdx.x < n_q) {
+        const int k = threadIdx.x;
+        double d = s_d[k][0];
+        long long i = s_i[k][0];
+        for (int w = 1; w < 8; w++) {
+            const double d2 = s_d[k][w];
+            const long long i2 = s_i[k][w];
+            if (i2 >= 0 && (i < 0 || d2 < d || (d2 == d && i2 < i))) { d = d2; i = i2; }
+        }
+        out_index[q0 + k] = i;                       // -1: no vertex on that layer
+        if (out_d2) out_d2[q0 + k] = d;
+    }
+}
+
+void pdn_nearest_vertex_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const int32_t *mesh_layer,
+                             const double *xy, int64_t n_q, const double *q_xy, const int32_t *q_layer,
+                             int64_t *out_index, double *out_d2, bool on_device) {
+    if (n_q == 0) return;
+    cudaStream_t st = ctx->stream;
+    int64_t n_v = 0;
+    if (on_device) {
+        PDN_CUDA(cudaMemcpyAsync(&n_v, v_off + n_mesh, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+    } else {
+        n_v = v_off[n_mesh];
+    }
+    DevIn<int64_t> d_voff;
+    DevIn<int32_t> d_ml, d_ql;
+    DevIn<double> d_xy, d_q;
+    DevBuf<int64_t> d_oi;
+    DevBuf<double> d_od;
+    d_voff.set(v_off, (size_t)n_mesh + 1, on_device, st);
+    d_ml.set(mesh_layer, (size_t)n_mesh, on_device, st);
+    d_xy.set(xy, (size_t)n_v * 2, on_device, st);
+    d_q.set(q_xy, (size_t)n_q * 2, on_device, st);
+    d_ql.set(q_layer, (size_t)n_q, on_device, st);
+    int64_t *oi = on_device ? out_index : d_oi.reserve((size_t)n_q);
+    double *od = out_d2 ? (on_device ? out_d2 : d_od.reserve((size_t)n_q)) : nullptr;
+    PDN_LAUNCH(ctx, nearest_vertex_kernel, pdn_blocks(n_q, NQ), 256, 0, n_mesh, d_voff.p, d_ml.p, (const double2 *)d_xy.p, n_q,
+               (const double2 *)d_q.p, d_ql.p, oi, od);
+    if (!on_device) {
+        PDN_CUDA(cudaMemcpyAsync(out_index, oi, (size_t)n_q * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        if (out_d2) PDN_CUDA(cudaMemcpyAsync(out_d2, od, (size_t)n_q * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
+    PDN_CUDA(cudaStreamSynchronize(st));
+}
+
 struct AssembleWork {
     DevIn<int64_t> d_voff, d_toff;
     DevIn<double> d_xy, d_cond, d_sval;

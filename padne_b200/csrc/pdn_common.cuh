@@ -234,6 +234,9 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
                        const double *s_val, const int32_t *s_op, bool on_device, int64_t *nnz_out);
 void pdn_element_weights_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, int64_t n_t,
                               const int32_t *tri, double *w, bool on_device);
+void pdn_nearest_vertex_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const int32_t *mesh_layer,
+                             const double *xy, int64_t n_q, const double *q_xy, const int32_t *q_layer,
+                             int64_t *out_index, double *out_d2, bool on_device);
 void pdn_power_density_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, const double *val,
                             int64_t n_t, const int32_t *tri, double conductivity, double *p,
                             bool on_device);

@@ -6,6 +6,7 @@ import pytest
 import scipy.sparse
 
 from conftest import golden_system_files, load_system
+from oracle import oracle
 from padne_b200 import solver as S
 from padne_b200 import synth
 
@@ -77,3 +78,53 @@ def test_solve_system_singular_behaves_like_superlu():
     with pytest.warns(Warning, match="exactly singular"):
         v, info = S.solve_system(L, r)
     assert np.isnan(v).all()
+
+
+# ---- row F3: nearest mesh vertex (pdn_nearest_vertex) ---------------------------------------------------
+def _golden_nearest():
+    import glob
+    return sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "nearest_*.npz")))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", _golden_nearest(), ids=os.path.basename)
+def test_nearest_vertex_golden(ctx, path):
+    d = np.load(path)                                  # expect: the reference's own KD-tree answers
+    idx, d2 = ctx.nearest_vertex(d["v_off"], d["mesh_layer"], d["xy"], d["q_xy"], d["q_layer"], return_d2=True)
+    assert np.array_equal(idx, d["expect"])
+    o_idx, o_d2 = oracle.nearest_vertex(d["v_off"], d["mesh_layer"], d["xy"], d["q_xy"], d["q_layer"])
+    assert np.array_equal(idx, o_idx) and np.array_equal(d2, o_d2)     # same rounding: bit-exact distances
+
+
+@pytest.mark.gpu
+def test_nearest_vertex_random_ties_empty(ctx):
+    rng = np.random.default_rng(9)
+    sizes = [5000, 1, 0, 3333, 777]                    # an empty mesh, a one-vertex mesh, two meshes on layer 4
+    mesh_layer = np.array([4, 0, 7, 4, 2], np.int32)
+    v_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    xy = np.round(rng.uniform(-3, 3, (v_off[-1], 2)), 1)          # a 0.1 lattice: plenty of exact ties and duplicates
+    q_xy = np.round(rng.uniform(-3.5, 3.5, (1003, 2)), 1) + rng.choice([0.0, 0.05], (1003, 2))
+    q_layer = rng.choice([0, 2, 4, 7, 9], 1003).astype(np.int32)   # 7: only an empty mesh; 9: no mesh at all
+    idx, d2 = ctx.nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer, return_d2=True)
+    o_idx, o_d2 = oracle.nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer)
+    assert np.array_equal(idx, o_idx)
+    assert np.array_equal(d2, o_d2)
+    assert np.all(idx[(q_layer == 7) | (q_layer == 9)] == -1)
+    assert ctx.nearest_vertex(v_off, mesh_layer, xy, np.zeros((0, 2)), np.zeros(0, np.int32)).shape == (0,)
+    with pytest.raises(ValueError):
+        ctx.nearest_vertex(v_off[:-1], mesh_layer, xy, q_xy, q_layer)
+
+
+@pytest.mark.gpu
+def test_nearest_vertex_full_size_property(ctx):
+    # BASELINE config 2 size: every vertex queried with itself must come back (distance 0), through 8-query tiles
+    fs = synth.board_2layer(708, n_via=16).to_flat()
+    v_off = np.asarray(fs.v_off, np.int64)
+    mesh_layer = np.arange(len(v_off) - 1, dtype=np.int32)
+    xy = np.asarray(fs.xy, np.float64).reshape(-1, 2)
+    sel = np.random.default_rng(0).choice(xy.shape[0], 4099, replace=False)
+    q_layer = (np.searchsorted(v_off, sel, side="right") - 1).astype(np.int32)
+    idx, d2 = ctx.nearest_vertex(v_off, mesh_layer, xy, xy[sel], q_layer, return_d2=True)
+    assert np.all(d2 == 0.0)
+    assert np.array_equal(xy[idx], xy[sel])            # the vertex itself, or an exact duplicate with a lower index
+    assert np.all(idx <= sel)

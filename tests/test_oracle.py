@@ -202,3 +202,50 @@ def test_corner_weights_match_laplace_offdiagonals():
     L = scipy.sparse.csr_matrix((d["data"], d["indices"], d["indptr"]), shape=(n, n))
     for (i, k), ws in acc.items():
         assert L[i, k] == sum(ws)
+
+
+# ---- row F3: nearest mesh vertex (NodeIndexer's KD-tree lookup) --------------------------------------
+def golden_nearest_files():
+    import glob
+    return sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "nearest_*.npz")))
+
+
+@pytest.mark.parametrize("path", golden_nearest_files(), ids=os.path.basename)
+def test_nearest_vertex_golden(path):
+    # expect = what the reference's own KD-trees returned (tests/golden/make_golden_nearest.py)
+    d = np.load(path)
+    idx, d2 = oracle.nearest_vertex(d["v_off"], d["mesh_layer"], d["xy"], d["q_xy"], d["q_layer"])
+    assert np.array_equal(idx, d["expect"])
+    assert np.all(d2 >= 0.0)
+
+
+def test_nearest_vertex_matches_scipy_kdtree():
+    # the reference's call (padne/solver.py:390-393, 424) on random clouds; two meshes share layer 1
+    import scipy.spatial
+    rng = np.random.default_rng(5)
+    sizes = [700, 450, 300, 1]
+    mesh_layer = np.array([0, 1, 1, 3], np.int32)
+    v_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    xy = rng.uniform(-5, 5, (v_off[-1], 2))
+    q_xy = rng.uniform(-6, 6, (500, 2))
+    q_layer = rng.choice([0, 1, 3], 500).astype(np.int32)
+    idx, d2 = oracle.nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer)
+    v_layer = np.repeat(mesh_layer, sizes)
+    for layer in (0, 1, 3):
+        members = np.flatnonzero(v_layer == layer)
+        tree = scipy.spatial.KDTree(xy[members], leafsize=32)
+        sel = np.flatnonzero(q_layer == layer)
+        dist, i = tree.query(q_xy[sel], k=1)
+        assert np.array_equal(idx[sel], members[i])
+        assert np.allclose(np.sqrt(d2[sel]), dist, rtol=1e-14, atol=0)
+
+
+def test_nearest_vertex_ties_and_empty_layer():
+    v_off = np.array([0, 4, 4, 6], np.int64)             # mesh 1 is empty
+    mesh_layer = np.array([0, 2, 0], np.int32)
+    xy = np.array([[0, 0], [1, 0], [1, 1], [0, 1], [2, 0.5], [0.5, 0.5]], float)
+    q_xy = np.array([[0.5, 0.0], [0.5, 0.5], [9, 9], [0.5, 0.5]], float)
+    q_layer = np.array([0, 0, 0, 2], np.int32)
+    idx, d2 = oracle.nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer)
+    assert idx.tolist() == [0, 5, 4, -1]                 # tie 0/1 -> lowest index; layer 2 has no vertex
+    assert d2[1] == 0.0 and np.isinf(d2[3])
