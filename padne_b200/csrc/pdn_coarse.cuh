@@ -69,8 +69,10 @@ __global__ void __launch_bounds__(CO_BLK) bbox_kernel(int64_t n_v, const double2
     }
 }
 
-// raw aggregate id of every reduced row (permuted numbering); -1 for rows the constraints eliminated
-__global__ void __launch_bounds__(CO_BLK) agg_raw_kernel(int64_t n, CoarseGeom g, const int64_t *__restrict__ v_off,
+// raw aggregate id of every reduced row (permuted numbering); -1 for rows the constraints eliminated and for
+// rows outside [row_lo, row_hi) (the rank-local level of a partitioned solve only aggregates its own rows)
+__global__ void __launch_bounds__(CO_BLK) agg_raw_kernel(int64_t n, int64_t row_lo, int64_t row_hi, CoarseGeom g,
+                                                         const int64_t *__restrict__ v_off,
                                                          const double2 *__restrict__ xy,
                                                          const int32_t *__restrict__ perm,
                                                          const int32_t *__restrict__ map, int32_t *__restrict__ raw,
@@ -78,7 +80,7 @@ __global__ void __launch_bounds__(CO_BLK) agg_raw_kernel(int64_t n, CoarseGeom g
     for (int64_t r = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; r < n; r += (int64_t)gridDim.x * CO_BLK) {
         const int32_t i = perm[r];
         int32_t a = -1;
-        if (map[i] == i) {
+        if (map[i] == i && r >= row_lo && r < row_hi) {
             if (i < g.n_v) {
                 int lo = 0, hi = g.n_mesh;          // largest m with v_off[m] <= i
                 while (hi - lo > 1) {
@@ -318,13 +320,21 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 // block reduction of CO_RB sums in a fixed order.
 constexpr int CO_RB = 4;
 constexpr int CO_JMAX = (CO_MAX + CO_BLK - 1) / CO_BLK;   // columns per thread
+// A second level (the rank-local one of a partitioned solve: nc2, Ainv2, rc_fix2, xc2) rides in the same
+// launch: the CTAs from grid1 on work on it.
 __global__ void __launch_bounds__(CO_BLK) coarse_apply_kernel(int32_t nc, const float *__restrict__ Ainv, const Scal *__restrict__ sc,
                                                               long long *__restrict__ rc_fix, double *__restrict__ xc,
-                                                              int slot, double boost) {
+                                                              int slot, double boost, int grid1, int32_t nc2,
+                                                              const float *__restrict__ Ainv2, long long *__restrict__ rc_fix2,
+                                                              double *__restrict__ xc2) {
     __shared__ double rcd[CO_MAX];
     __shared__ double red[CO_RB][CO_BLK / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int row0 = blockIdx.x * CO_RB;
+    int row0 = blockIdx.x * CO_RB;
+    if ((int)blockIdx.x >= grid1) {
+        row0 = ((int)blockIdx.x - grid1) * CO_RB;
+        nc = nc2; Ainv = Ainv2; rc_fix = rc_fix2; xc = xc2;
+    }
     // the matrix entries do not depend on anything this iteration produced: request them first
     float a[CO_RB][CO_JMAX];
 #pragma unroll
@@ -378,7 +388,8 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
                                                        const int32_t *__restrict__ agg, const double *__restrict__ xc,
                                                        double *__restrict__ z, const PeerLink *Lp, const HaloSend *hsp,
                                                        size_t vec_off, const int32_t *__restrict__ send_idx,
-                                                       unsigned int *ticket) {
+                                                       unsigned int *ticket, const int32_t *__restrict__ agg2,
+                                                       const double *__restrict__ xc2) {
     pdl_trigger();
     pdl_wait();
     if (sc->done) return;
@@ -390,11 +401,23 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
             const double2 dd = *reinterpret_cast<const double2 *>(dinv + i), rr = *reinterpret_cast<const double2 *>(r + i);
             const int2 aa = *reinterpret_cast<const int2 *>(agg + i);
             const double ca = aa.x >= 0 ? __ldg(&xc[aa.x]) : 0.0;
-            const double cb = aa.y == aa.x ? ca : (aa.y >= 0 ? __ldg(&xc[aa.y]) : 0.0);
-            *reinterpret_cast<double2 *>(z + i) = make_double2(dd.x * rr.x + ca, dd.y * rr.y + cb);
+            double cb = aa.y == aa.x ? ca : (aa.y >= 0 ? __ldg(&xc[aa.y]) : 0.0);
+            double ca2 = ca;
+            if (agg2 != nullptr) {          // rank-local second level
+                const int2 bb = *reinterpret_cast<const int2 *>(agg2 + i);
+                const double la = bb.x >= 0 ? __ldg(&xc2[bb.x]) : 0.0;
+                ca2 += la;
+                cb += bb.y == bb.x ? la : (bb.y >= 0 ? __ldg(&xc2[bb.y]) : 0.0);
+            }
+            *reinterpret_cast<double2 *>(z + i) = make_double2(dd.x * rr.x + ca2, dd.y * rr.y + cb);
         } else {
             const int32_t a = agg[i];
-            z[i] = dinv[i] * r[i] + (a >= 0 ? __ldg(&xc[a]) : 0.0);
+            double c = a >= 0 ? __ldg(&xc[a]) : 0.0;
+            if (agg2 != nullptr) {
+                const int32_t b = agg2[i];
+                c += b >= 0 ? __ldg(&xc2[b]) : 0.0;
+            }
+            z[i] = dinv[i] * r[i] + c;
         }
     }
     if (BLK != 1024 || Lp == nullptr) return;    // the tail only exists in the multi-GPU instantiation

@@ -229,16 +229,20 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
                                                               double *__restrict__ p, double *__restrict__ s,
                                                               double *__restrict__ x, double *__restrict__ r,
                                                               const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc,
-                                                              const PeerLink *Lp, unsigned int *ticket) {
+                                                              const PeerLink *Lp, unsigned int *ticket,
+                                                              const int32_t *__restrict__ agg2, long long *rc_fix2, int32_t nc2) {
     __shared__ long long tab[CO_MAX];
+    __shared__ long long tab2[CO_MAX];   // rank-local second level (nc2 == 0: none)
     pdl_trigger();
     for (int a = threadIdx.x; a < nc; a += TLB) tab[a] = 0;
+    for (int a = threadIdx.x; a < nc2; a += TLB) tab2[a] = 0;
     pdl_wait();
     if (sc->done) return;
     if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 6);
     const double alpha = sc->alpha, beta = sc->beta;
     const double fix = CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300));
     unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc;
+    unsigned long long *rc2 = nc2 > 0 ? reinterpret_cast<unsigned long long *>(rc_fix2) + (size_t)(sc->iter & 1) * nc2 : nullptr;
     const int64_t npair = (n - r0 + 1) >> 1;
     const int64_t per = ((npair + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;   // whole warps
     const int64_t t_lo = (int64_t)blockIdx.x * per, t_hi = t_lo + per < npair ? t_lo + per : npair;
@@ -290,11 +294,40 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
             if (lane == __ffs(peers) - 1 && a1 >= 0 && sum != 0)
                 atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a1]), (unsigned long long)(long long)sum);
         }
+        if (nc2 > 0) {   // the same entries into the rank-local level's table
+            int32_t b0 = -1, b1 = -1;
+            if (full) {
+                const int2 bb = *reinterpret_cast<const int2 *>(agg2 + i);
+                b0 = bb.x;
+                b1 = bb.y;
+            } else if (act) {
+                b0 = agg2[i];
+            }
+            int p0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
+            int p1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
+            if (b1 == b0) { p0 += p1; b1 = -1; }
+            {
+                const unsigned peers = __match_any_sync(0xffffffffu, b0);
+                const int sum = __reduce_add_sync(peers, p0);
+                if (lane == __ffs(peers) - 1 && b0 >= 0 && sum != 0)
+                    atomicAdd(reinterpret_cast<unsigned long long *>(&tab2[b0]), (unsigned long long)(long long)sum);
+            }
+            if (__any_sync(0xffffffffu, b1 >= 0)) {
+                const unsigned peers = __match_any_sync(0xffffffffu, b1);
+                const int sum = __reduce_add_sync(peers, p1);
+                if (lane == __ffs(peers) - 1 && b1 >= 0 && sum != 0)
+                    atomicAdd(reinterpret_cast<unsigned long long *>(&tab2[b1]), (unsigned long long)(long long)sum);
+            }
+        }
     }
     __syncthreads();
     for (int a = threadIdx.x; a < nc; a += TLB) {
         const long long v = tab[a];
         if (v != 0) atomicAdd(&rc[a], (unsigned long long)v);
+    }
+    for (int a = threadIdx.x; a < nc2; a += TLB) {
+        const long long v = tab2[a];
+        if (v != 0) atomicAdd(&rc2[a], (unsigned long long)v);
     }
     if (Lp == nullptr) return;
     // several GPUs: the last CTA to finish sums r_c over the ranks (peer-memory stores, pdn_peer_prim.cuh)

@@ -165,6 +165,13 @@ struct SolveWork {
     DevBuf<long long> co_acc, rc_fix;
     DevBuf<double> co_A, co_piv, xc, co_tmp;
     DevBuf<float> co_Af;
+    // rank-local second coarse level of a partitioned PCG solve (aggregates over this rank's rows only, finer
+    // bins, block-diagonal: couplings to other ranks' rows are dropped; no exchange)
+    DevBuf<int32_t> agg2;
+    DevBuf<long long> rc_fix2;
+    DevBuf<double> co_A2, xc2;
+    DevBuf<float> co_Af2;
+    int32_t nc2 = 0;
     DevBuf<unsigned int> co_counter;
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
@@ -579,7 +586,7 @@ static bool halo_in_coarse_z(pdn_ctx *ctx, SolveWork *w) {
 }
 
 void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, double boost, const double *src,
-                               double *dst, bool rc_summed = false) {
+                               double *dst, bool rc_summed = false, bool with_local = false) {
     // several GPUs: every rank restricted its own rows -> exact integer sum, identical everywhere.  NCCL
     // fallback: both slots (the idle one is all zeros).  Peer memory: cg_update_tl_kernel's last CTA has already
     // done it (rc_summed); the other restricting kernels are followed by the exchange kernel.
@@ -589,8 +596,12 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
             PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, slot);
     }
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
-    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply_kernel, cgrid, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_fix.p, w->xc.p, slot,
-                   boost);
+    const int32_t nc2 = with_local ? w->nc2 : 0;
+    const int cgrid2 = (nc2 + CO_RB - 1) / CO_RB;
+    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply_kernel, cgrid + cgrid2, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_fix.p, w->xc.p,
+                   slot, boost, cgrid, nc2, w->co_Af2.p, w->rc_fix2.p, w->xc2.p);
+    const int32_t *agg2 = nc2 > 0 ? w->agg2.p : nullptr;
+    const double *xc2 = nc2 > 0 ? w->xc2.p : nullptr;
     const PeerLink *Lp = nullptr;
     size_t vec_off = 0;
     unsigned int *ticket = nullptr;
@@ -607,10 +618,10 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
         const int64_t npair = (w->row_end - w->row_begin + 1) / 2;
         const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));   // one CTA per SM (60 registers)
         PDN_LAUNCH(ctx, coarse_z_kernel<1024>, zgrid, 1024, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p, src, w->agg.p,
-                   w->xc.p, dst, Lp, w->halo.peer_d.p, vec_off, w->halo.send_idx.p, ticket);
+                   w->xc.p, dst, Lp, w->halo.peer_d.p, vec_off, w->halo.send_idx.p, ticket, agg2, xc2);
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, coarse_z_kernel<CO_BLK>, vgrid, CO_BLK, 0, w->row_begin, w->row_end, w->d_sc, w->dinv.p,
-                       src, w->agg.p, w->xc.p, dst, Lp, (const HaloSend *)nullptr, vec_off, w->halo.send_idx.p, ticket);
+                       src, w->agg.p, w->xc.p, dst, Lp, (const HaloSend *)nullptr, vec_off, w->halo.send_idx.p, ticket, agg2, xc2);
     }
 }
 
@@ -627,8 +638,10 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         }
         const int tgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * tl_per_sm, (npair + TLB - 1) / TLB));
         PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_tl_kernel, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
-                       w->r.p, w->agg.p, w->rc_fix.p, w->nc, peer_link_or_none(ctx), &w->d_sc->ticket[3]);
-        enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, /*rc_summed=*/pdn_peer_enabled(ctx));
+                       w->r.p, w->agg.p, w->rc_fix.p, w->nc, peer_link_or_none(ctx), &w->d_sc->ticket[3],
+                       w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p, w->nc2);
+        enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, /*rc_summed=*/pdn_peer_enabled(ctx),
+                                  /*with_local=*/true);
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p, w->p.p, w->s.p,
                    w->x.p, w->r.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
@@ -765,7 +778,12 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
                 PDN_LAUNCH(ctx, cg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
                            w->s.p, w->agg.p, w->rc_fix.p, w->nc);
-                enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p);
+                if (w->nc2 > 0) {   // the same restriction into the rank-local level
+                    PDN_CUDA(cudaMemsetAsync(w->rc_fix2.p, 0, (size_t)2 * w->nc2 * sizeof(long long), st));
+                    PDN_LAUNCH(ctx, cg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
+                               w->s.p, w->agg2.p, w->rc_fix2.p, w->nc2);
+                }
+                enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, false, /*with_local=*/true);
             } else if (method == PDN_METHOD_PCG) {
                 PDN_LAUNCH(ctx, cg_init_kernel<false>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
                            w->s.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
@@ -1029,17 +1047,29 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
 // two-level preconditioner: aggregates, coarse matrix, its inverse (kernels in pdn_coarse.cuh).
 // Returns false (and leaves Jacobi in place) when no useful coarse space can be built.
 // ------------------------------------------------------------------------------------------------
-static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_entries, bool symmetric) {
+// local == false: the global level over all rows (replicated on every rank).
+// local == true:  the rank-local level: bins `world` times finer, only the rows [row_begin, row_end) get an
+//                 aggregate, so A_loc = P^T A P keeps the couplings inside this rank only.
+static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_entries, bool symmetric, bool local = false) {
     cudaStream_t st = ctx->stream;
     const int64_t n = w->n;
-    w->two_level = false;
-    w->nc = 0;
+    DevBuf<int32_t> &agg = local ? w->agg2 : w->agg;
+    DevBuf<long long> &rc_fix = local ? w->rc_fix2 : w->rc_fix;
+    DevBuf<double> &co_A = local ? w->co_A2 : w->co_A;
+    DevBuf<double> &xc = local ? w->xc2 : w->xc;
+    DevBuf<float> &co_Af = local ? w->co_Af2 : w->co_Af;
+    const int64_t row_lo = local ? w->row_begin : 0, row_hi = local ? w->row_end : n;
+    const int world = local ? std::max(1, w->halo.world) : 1;
+    if (local) w->nc2 = 0;
+    else { w->two_level = false; w->nc = 0; }
     if (!ctx->geo_valid || ctx->geo_n_v <= 0 || ctx->geo_n_v > n) return false;
     // default: the inverse costs ~2.5 ms at 1600 aggregates and buys ~20% fewer iterations than 1024 at 1M rows
     if (target <= 0) target = n >= 200000 ? 1600 : 1024;
     if (target > CO_MAX) target = CO_MAX;
-    if (target > n / 16) target = (int32_t)(n / 16);     // tiny systems: keep >= 16 rows per aggregate
+    if (target > (row_hi - row_lo) / 16) target = (int32_t)((row_hi - row_lo) / 16);     // tiny systems: keep >= 16 rows per aggregate
     if (target < 4) return false;
+    // bins are laid over ALL meshes; the local level keeps the ~1/world of them that hold its rows
+    const int64_t raw_target = (int64_t)target * world;
 
     // bounding box of the vertices
     const int bgrid = pdn_grid(ctx, ctx->geo_n_v, CO_BLK, 4);
@@ -1063,32 +1093,37 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     g.node_group = n_internal > 256 ? (int32_t)((n_internal + 255) / 256) : 1;
     const int32_t node_aggs = (int32_t)((n_internal + g.node_group - 1) / g.node_group);
     const double W = std::max(x1 - x0, 1e-12), Ht = std::max(y1 - y0, 1e-12);
-    double bins_per_mesh = std::max(1.0, (double)(target - node_aggs) / g.n_mesh);
+    double bins_per_mesh = std::max(1.0, (double)(raw_target - node_aggs) / g.n_mesh);
     double H = sqrt(W * Ht / bins_per_mesh);
-    for (int guard = 0; guard < 200; guard++) {
-        g.nbx = std::max(1, (int)ceil(W / H));
-        g.nby = std::max(1, (int)ceil(Ht / H));
-        if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs <= std::max<int64_t>(target, 4)) break;
-        H *= 1.05;
-    }
-    if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs > CO_MAX) return false;
-    g.x0 = x0; g.y0 = y0; g.inv_h = 1.0 / H;
-    g.n_bins = g.n_mesh * g.nbx * g.nby;
-    const int32_t n_raw = g.n_bins + node_aggs;
-
-    // aggregate ids: raw bin -> compact id over the non-empty bins
-    w->agg.reserve((size_t)n);
-    w->co_used.reserve((size_t)n_raw + 1);
-    w->co_cid.reserve((size_t)n_raw + 1);
-    PDN_CUDA(cudaMemsetAsync(w->co_used.p, 0, ((size_t)n_raw + 1) * sizeof(int32_t), st));
-    PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, g, ctx->geo_voff.p,
-               (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, w->agg.p, w->co_used.p);
-    pdn_exclusive_scan_i32(ctx, w->co_used.p, n_raw, w->co_cid.p);
     int32_t nc = 0;
-    PDN_CUDA(cudaMemcpyAsync(&nc, w->co_cid.p + n_raw, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    PDN_CUDA(cudaStreamSynchronize(st));
-    if (nc < 2 || nc > CO_MAX) return false;
-    PDN_LAUNCH(ctx, agg_final_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->co_cid.p, w->agg.p);
+    agg.reserve((size_t)n);
+    for (int attempt = 0;; attempt++) {
+        for (int guard = 0; guard < 200; guard++) {
+            g.nbx = std::max(1, (int)ceil(W / H));
+            g.nby = std::max(1, (int)ceil(Ht / H));
+            if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs <= std::max<int64_t>(raw_target, 4)) break;
+            H *= 1.05;
+        }
+        if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs > (int64_t)CO_MAX * world) return false;
+        g.x0 = x0; g.y0 = y0; g.inv_h = 1.0 / H;
+        g.n_bins = g.n_mesh * g.nbx * g.nby;
+        const int32_t n_raw = g.n_bins + node_aggs;
+
+        // aggregate ids: raw bin -> compact id over the non-empty bins
+        w->co_used.reserve((size_t)n_raw + 1);
+        w->co_cid.reserve((size_t)n_raw + 1);
+        PDN_CUDA(cudaMemsetAsync(w->co_used.p, 0, ((size_t)n_raw + 1) * sizeof(int32_t), st));
+        PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, row_lo, row_hi, g, ctx->geo_voff.p,
+                   (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, agg.p, w->co_used.p);
+        pdn_exclusive_scan_i32(ctx, w->co_used.p, n_raw, w->co_cid.p);
+        PDN_CUDA(cudaMemcpyAsync(&nc, w->co_cid.p + n_raw, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        if (nc < 2) return false;
+        if (nc <= CO_MAX) break;
+        if (!local || attempt >= 6) return false;
+        H *= 1.15;              // an uneven partition put more bins on this rank than the table holds: coarser bins
+    }
+    PDN_LAUNCH(ctx, agg_final_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->co_cid.p, agg.p);
 
     // fixed-point scale of A_c: |sum| <= entries * largest diagonal must stay below 2^62
     const int mgrid = pdn_grid(ctx, n, CO_BLK, 4);
@@ -1104,15 +1139,15 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
 
     const size_t nc2 = (size_t)nc * nc;
     w->co_acc.reserve(nc2);
-    w->co_A.reserve(nc2);
+    co_A.reserve(nc2);
     PDN_CUDA(cudaMemsetAsync(w->co_acc.p, 0, nc2 * sizeof(long long), st));
-    PDN_LAUNCH(ctx, coarse_accum_kernel, pdn_grid(ctx, w->n_slices * 32, CO_BLK, 8), CO_BLK, 0, w->A, w->n_slices, w->agg.p,
+    PDN_LAUNCH(ctx, coarse_accum_kernel, pdn_grid(ctx, w->n_slices * 32, CO_BLK, 8), CO_BLK, 0, w->A, w->n_slices, agg.p,
                nc, fix, (unsigned long long *)w->co_acc.p);
     if (w->A.n_special > 0)
-        PDN_LAUNCH(ctx, coarse_accum_special_kernel, pdn_blocks(w->A.n_special, CO_BLK), CO_BLK, 0, w->A, w->agg.p, nc, fix,
+        PDN_LAUNCH(ctx, coarse_accum_special_kernel, pdn_blocks(w->A.n_special, CO_BLK), CO_BLK, 0, w->A, agg.p, nc, fix,
                    (unsigned long long *)w->co_acc.p);
     PDN_LAUNCH(ctx, coarse_convert_kernel, pdn_grid(ctx, (int64_t)nc2, CO_BLK, 8), CO_BLK, 0, nc, 1.0 / fix, w->co_acc.p,
-               w->co_A.p, symmetric ? 1 : 0);
+               co_A.p, symmetric ? 1 : 0);
 
     // inverse: cooperative blocked Gauss-Jordan, rows of the matrix resident in shared memory
     // rows per CTA: the critical path is one R x R inverse + one rank-R update + one flag hand-over per
@@ -1135,11 +1170,11 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     pdn_status_reset(ctx);
     {
         int32_t nc_arg = nc, R_arg = R;
-        double *A_arg = w->co_A.p, *piv_arg = w->co_piv.p;
+        double *A_arg = co_A.p, *piv_arg = w->co_piv.p;
         unsigned int *cnt_arg = w->co_counter.p;
         int32_t *st_arg = ctx->d_status;
-        w->co_Af.reserve(nc2);
-        float *af_arg = w->co_Af.p;
+        co_Af.reserve(nc2);
+        float *af_arg = co_Af.p;
         void *args[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg, &af_arg};
         PDN_CUDA(cudaLaunchCooperativeKernel((void *)coarse_invert_kernel, dim3(grid), dim3(CO_BLK), args, smem, st));
         ctx->launches++;
@@ -1151,10 +1186,14 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         ctx->last_error = std::string("coarse matrix inversion failed (") + pdn_strerror(stt) + "): Jacobi only";
         return false;
     }
-    w->rc_fix.reserve((size_t)2 * nc);
-    w->xc.reserve((size_t)nc);
-    w->nc = nc;
-    w->two_level = true;
+    rc_fix.reserve((size_t)2 * nc);
+    xc.reserve((size_t)nc);
+    if (local) {
+        w->nc2 = nc;
+    } else {
+        w->nc = nc;
+        w->two_level = true;
+    }
     return true;
 }
 
@@ -1496,6 +1535,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     // second level of the preconditioner (systems assembled from meshes: the aggregates are coordinate bins)
     w->two_level = false;
     w->nc = 0;
+    w->nc2 = 0;
     w->coarse_ms = 0.f;
     {
         const bool want = opts.precond == PDN_PRECOND_TWOLEVEL || (opts.precond == PDN_PRECOND_AUTO && n >= 1024);
@@ -1521,6 +1561,23 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             cudaEventDestroy(c1);
             if (!ok && opts.precond == PDN_PRECOND_TWOLEVEL)
                 PDN_FAIL(PDN_EUNSUPPORTED, "solve: no coarse space could be built (%s)", ctx->last_error.c_str());
+            // several GPUs, PCG: a second, rank-local level keeps the bins as fine as on one GPU (the global level
+            // is capped at CO_MAX aggregates for the whole board); every rank must take the same decision,
+            // so a rank whose local level cannot be built runs with nc2 = 0 but still launches the same kernels
+            w->nc2 = 0;
+            // Measured: on 2 GPUs it saves 16 % of the iterations but costs 20 % per iteration (second restriction
+            // and apply), so it is the default from 4 ranks on; PADNE_B200_LOCAL_LEVEL=0/1 overrides (same on all ranks).
+            const char *le = getenv("PADNE_B200_LOCAL_LEVEL");
+            const bool want_local = le ? le[0] != '0' : pdn_comm_world(ctx) >= 4;
+            if (ok && is_dist(ctx) && method == PDN_METHOD_PCG && want_local) {
+                try {
+                    build_coarse(ctx, w, opts.n_coarse, (int64_t)sell_total + (int64_t)r_ci.size(), E.symmetric, /*local=*/true);
+                } catch (...) {
+                    cudaEventDestroy(c0);
+                    cudaEventDestroy(c1);
+                    throw;
+                }
+            }
         }
     }
 

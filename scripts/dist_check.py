@@ -49,7 +49,10 @@ for name, grid in zip(cases[0::2], cases[1::2]):
     # PCG takes the identical iteration path on any number of ranks (1e-9); BiCGSTAB is
     # sensitive to the summation order of its dot products, so two converged runs only agree to the
     # accuracy the 1e-10 residual buys (measured 8e-9)
-    tol = 1e-9 if i2.method == "pcg" else 1e-7
+    # With the rank-local coarse level (default on several GPUs) the preconditioner, hence the iteration path,
+    # depends on the partition: PADNE_B200_LOCAL_LEVEL=0 restores the identical path and the 1e-9 bound.
+    same_path = i2.method == "pcg" and os.environ.get("PADNE_B200_LOCAL_LEVEL", "1" if world >= 4 else "0")[:1] == "0"
+    tol = 1e-9 if same_path else 1e-7
     good = err < tol and bool(flag.item()) and i2.rel_residual <= 1.05e-10
     ok = ok and good
     if rank == 0:
