@@ -224,6 +224,8 @@ __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, c
 // flushes its non-zero entries at the end: ~2K global atomics per launch.  1024 threads per CTA, two CTAs per
 // SM, so that the table is cleared and flushed by two entries per thread.
 constexpr int TLB = 1024;
+// LOCAL: also restrict into the rank-local second level (partitioned solves from 4 ranks on)
+template <bool LOCAL>
 __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
                                                               const double *__restrict__ w, const double *__restrict__ z,
                                                               double *__restrict__ p, double *__restrict__ s,
@@ -232,17 +234,18 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
                                                               const PeerLink *Lp, unsigned int *ticket,
                                                               const int32_t *__restrict__ agg2, long long *rc_fix2, int32_t nc2) {
     __shared__ long long tab[CO_MAX];
-    __shared__ long long tab2[CO_MAX];   // rank-local second level (nc2 == 0: none)
+    __shared__ long long tab2[LOCAL ? CO_MAX : 1];   // rank-local second level
     pdl_trigger();
     for (int a = threadIdx.x; a < nc; a += TLB) tab[a] = 0;
-    for (int a = threadIdx.x; a < nc2; a += TLB) tab2[a] = 0;
+    if (LOCAL)
+        for (int a = threadIdx.x; a < nc2; a += TLB) tab2[a] = 0;
     pdl_wait();
     if (sc->done) return;
     if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 6);
     const double alpha = sc->alpha, beta = sc->beta;
     const double fix = CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300));
     unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix) + (size_t)(sc->iter & 1) * nc;
-    unsigned long long *rc2 = nc2 > 0 ? reinterpret_cast<unsigned long long *>(rc_fix2) + (size_t)(sc->iter & 1) * nc2 : nullptr;
+    unsigned long long *rc2 = LOCAL ? reinterpret_cast<unsigned long long *>(rc_fix2) + (size_t)(sc->iter & 1) * nc2 : nullptr;
     const int64_t npair = (n - r0 + 1) >> 1;
     const int64_t per = ((npair + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;   // whole warps
     const int64_t t_lo = (int64_t)blockIdx.x * per, t_hi = t_lo + per < npair ? t_lo + per : npair;
@@ -294,7 +297,7 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
             if (lane == __ffs(peers) - 1 && a1 >= 0 && sum != 0)
                 atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a1]), (unsigned long long)(long long)sum);
         }
-        if (nc2 > 0) {   // the same entries into the rank-local level's table
+        if (LOCAL) {   // the same entries into the rank-local level's table
             int32_t b0 = -1, b1 = -1;
             if (full) {
                 const int2 bb = *reinterpret_cast<const int2 *>(agg2 + i);
@@ -325,7 +328,7 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
         const long long v = tab[a];
         if (v != 0) atomicAdd(&rc[a], (unsigned long long)v);
     }
-    for (int a = threadIdx.x; a < nc2; a += TLB) {
+    for (int a = threadIdx.x; LOCAL && a < nc2; a += TLB) {
         const long long v = tab2[a];
         if (v != 0) atomicAdd(&rc2[a], (unsigned long long)v);
     }

@@ -631,13 +631,12 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     launch_sell<CG>(ctx, w, w->z.p, w->w.p, w->r.p);
     if (w->two_level) {
         const int64_t npair = (r1 - r0 + 1) / 2;
-        static int tl_per_sm = 0;
-        if (!tl_per_sm) {
-            PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&tl_per_sm, cg_update_tl_kernel, TLB, 0));
-            if (tl_per_sm < 1) tl_per_sm = 1;
-        }
+        auto kern = w->nc2 > 0 ? cg_update_tl_kernel<true> : cg_update_tl_kernel<false>;
+        int tl_per_sm = 1;
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&tl_per_sm, kern, TLB, 0));
+        if (tl_per_sm < 1) tl_per_sm = 1;
         const int tgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * tl_per_sm, (npair + TLB - 1) / TLB));
-        PDN_LAUNCH_PDL(ctx, w->pdl, cg_update_tl_kernel, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
+        PDN_LAUNCH_PDL(ctx, w->pdl, kern, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
                        w->r.p, w->agg.p, w->rc_fix.p, w->nc, peer_link_or_none(ctx), &w->d_sc->ticket[3],
                        w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p, w->nc2);
         enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, /*rc_summed=*/pdn_peer_enabled(ctx),
