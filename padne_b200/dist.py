@@ -78,3 +78,19 @@ def init_comm(ctx, group=None) -> tuple[int, int]:
     uid = broadcast_unique_id(type(ctx).comm_unique_id, rank, group)
     ctx.comm_init(rank, world, uid)
     return rank, world
+
+
+def local_level_aggregates(begin: np.ndarray, me: int, raw_bin: np.ndarray) -> tuple[np.ndarray, int]:
+    """Aggregate ids of the rank-local second coarse level (``build_coarse(..., local=true)`` in
+    ``csrc/pdn_solve.cu``), restated for host code and tests: every row owned by rank ``me`` keeps its
+    (fine) coordinate bin ``raw_bin[row]`` (negative = none: a row the constraints eliminated), rows of
+    other ranks get -1, and the surviving bins are renumbered compactly in ascending bin order.  The
+    level ``P_k (P_k^T A P_k)^-1 P_k^T`` built from these ids only couples rows of rank ``me``, which is why it
+    needs no exchange.  Returns (agg [n], number of aggregates)."""
+    raw_bin = np.asarray(raw_bin, np.int64)
+    rows = np.arange(raw_bin.shape[0])
+    mine = (rows >= begin[me]) & (rows < begin[me + 1]) & (raw_bin >= 0)
+    agg = np.full(raw_bin.shape[0], -1, np.int64)
+    used = np.unique(raw_bin[mine])
+    agg[mine] = np.searchsorted(used, raw_bin[mine])
+    return agg, int(used.shape[0])
