@@ -52,10 +52,11 @@ extern "C" {
 
 /* preconditioners */
 #define PDN_PRECOND_AUTO 0      /* two-level when the system came from pdn_assemble (coordinates are
-                                   resident) and is symmetric, else Jacobi                              */
+                                   resident) and has >= 1024 rows, else Jacobi                          */
 #define PDN_PRECOND_NONE 1
 #define PDN_PRECOND_AMG 2       /* reserved (multilevel aggregation); pdn_solve answers PDN_EUNSUPPORTED */
-#define PDN_PRECOND_TWOLEVEL 3  /* Jacobi + coarse space of piecewise constants over coordinate bins    */
+#define PDN_PRECOND_TWOLEVEL 3  /* Jacobi + coarse space of piecewise constants over coordinate bins (PCG
+                                   and BiCGSTAB); partitioned PCG adds a rank-local level from 4 ranks  */
 #define PDN_PRECOND_JACOBI 4
 
 typedef struct pdn_ctx pdn_ctx;
@@ -138,7 +139,7 @@ int pdn_set_csr(pdn_ctx *ctx, int64_t N, int64_t nnz, const int32_t *indptr, con
 /* ---- kernels (3)+(4): the solve ------------------------------------------------------------------
  * Replaces solve_system (padne/solver.py:767-780): solves L v = rhs for the resident L.
  * The constraint rows/columns (indices >= n_nodes) are eliminated on the host (union-find with
- * voltage offsets), the reduced operator is solved with Jacobi-PCG (symmetric) or BiCGSTAB
+ * voltage offsets), the reduced operator is solved with preconditioned CG (symmetric) or BiCGSTAB
  * (regulator gains present), the eliminated currents are recovered, and the residual of the
  * FULL system is reported exactly as solver.py:775.   rhs [N], v [N]. */
 int pdn_solve(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts, double *v, pdn_info *info,
