@@ -266,6 +266,62 @@ def produce_layer_solutions(layers, vindex, meshes, mesh_index_to_layer_index, v
 
 
 # ------------------------------------------------------------------------------------------------
+# row F3: NodeIndexer with the nearest-vertex lookup on the GPU
+# ------------------------------------------------------------------------------------------------
+class _PrecomputedTree:
+    """Stands in for one per-layer ``scipy.spatial.KDTree`` inside the reference's ``NodeIndexer.create``:
+    ``query((x, y), k=1)`` answers from the batch that ``pdn_nearest_vertex`` already computed."""
+
+    def __init__(self):
+        self.answers = {}
+
+    def query(self, point, k=1):
+        return 0.0, self.answers[(float(point[0]), float(point[1]))]
+
+
+class _IdentityIndex:
+    """``layer_global_index_and_vertex[layer][i][0]`` of the reference, for trees that already answer with the
+    global vertex index."""
+
+    def __getitem__(self, i):
+        return (int(i), None)
+
+
+def node_indexer_create(ref, prob, meshes, mesh_index_to_layer_index, vindex, filtered_networks,
+                        ctx: Optional[capi.Context] = None, lookup=None):
+    """``NodeIndexer.create`` (``padne/solver.py:399-466``) with its KD-trees replaced by ONE call of
+    ``pdn_nearest_vertex`` for all connections.
+
+    The reference's own ``create`` still runs -- the duplicate check and the numbering of the internal
+    nodes (which follows ``set`` iteration over identity-hashed ``NodeID``s) stay its code; only
+    ``_construct_kdtrees`` (``:356-396``) is swapped, for the duration of the call, for objects that
+    answer ``kdtree.query`` (``:424``) from the precomputed batch.  ``lookup(v_off, mesh_layer, xy, q_xy,
+    q_layer) -> global indices`` defaults to the GPU; tests inject the oracle."""
+    if lookup is None:
+        lookup = (ctx or capi.default_context(OPTIONS.device)).nearest_vertex
+    conns = [c for net in filtered_networks for c in net.connections]
+    v_off = np.concatenate([[0], np.cumsum([len(m.vertices) for m in meshes])]).astype(np.int64)
+    xy = np.array([(v.p.x, v.p.y) for m in meshes for v in m.vertices], np.float64).reshape(-1, 2)
+    q_xy = np.array([(c.point.x, c.point.y) for c in conns], np.float64).reshape(-1, 2)
+    q_layer = np.array([prob.layers.index(c.layer) for c in conns], np.int32)
+    idx = lookup(v_off, np.asarray(mesh_index_to_layer_index, np.int32), xy, q_xy, q_layer) if len(conns) else []
+    trees, index_lists = {}, {}
+    for layer_i in set(int(l) for l in mesh_index_to_layer_index):
+        if any(len(m.vertices) for m, l in zip(meshes, mesh_index_to_layer_index) if l == layer_i):
+            trees[layer_i] = _PrecomputedTree()           # an empty layer gets none, like the reference (:381-386)
+            index_lists[layer_i] = _IdentityIndex()
+    for c, layer_i, g in zip(conns, q_layer, idx):
+        if int(g) >= 0:
+            trees[int(layer_i)].answers[(float(c.point.x), float(c.point.y))] = int(g)
+    original = ref.NodeIndexer.__dict__["_construct_kdtrees"]
+    ref.NodeIndexer._construct_kdtrees = classmethod(lambda cls, *a, **k: (trees, index_lists))
+    try:
+        return ref.NodeIndexer.create(prob, meshes, mesh_index_to_layer_index, vindex, filtered_networks)
+    finally:
+        ref.NodeIndexer._construct_kdtrees = original
+
+
+# ------------------------------------------------------------------------------------------------
 # the public entry point
 # ------------------------------------------------------------------------------------------------
 def solve_meshed(prob, meshes, mesh_index_to_layer_index, disconnected_meshes_by_layer=None,
@@ -281,7 +337,7 @@ def solve_meshed(prob, meshes, mesh_index_to_layer_index, disconnected_meshes_by
     if filtered_networks is None:
         filtered_networks = list(prob.networks)
     log.info("Constructing node index for networks")
-    node_indexer = ref.NodeIndexer.create(prob, meshes, mesh_index_to_layer_index, vindex, filtered_networks)
+    node_indexer = node_indexer_create(ref, prob, meshes, mesh_index_to_layer_index, vindex, filtered_networks, ctx)
     log.info("Assembling the global system")
     L, r = assemble_system(prob, meshes, mesh_index_to_layer_index, vindex, filtered_networks, node_indexer, ctx)
     log.info("Solving the system of equations")

@@ -134,3 +134,36 @@ def test_stamp_network_into_system_host_mirror():
     expect = np.array([[-g, g, -1.0], [g, -g, 1.0], [-1.0, 1.0, 0.0]])
     assert np.array_equal(L.toarray(), expect)
     assert np.array_equal(r, [0.0, 0.0, 3.3])
+
+
+def test_node_indexer_create_with_batched_lookup():
+    # Row F3 drop-in: the reference's own NodeIndexer.create, its KD-trees swapped for one batched lookup
+    # (the oracle stands in for the GPU here), must number every node exactly like the stock create().
+    # Needs the reference importable (build container only); nothing is read from it on the GPU box.
+    from oracle import refload
+    if not refload.reference_available():
+        pytest.skip("reference not present")
+    from oracle import oracle
+    from padne_b200 import solver as S
+    problem, mesh, ref = refload.load_reference()
+    import shapely.geometry as geometry
+    for board in (synth.board_4layer_regulator(20, n_via=2, size_mm=8.0, seed=4),
+                  synth.board_via_tht_standin(20, seed=1, n_via=2)):
+        prob, meshes, m2l = synth.to_reference_objects(board, problem, mesh, geometry)
+        vindex = ref.VertexIndexer.create(meshes)
+        nets = list(prob.networks)
+        stock = ref.NodeIndexer.create(prob, meshes, m2l, vindex, nets)
+        calls = []
+
+        def lookup(*a):
+            calls.append(len(a[3]))
+            return oracle.nearest_vertex(*a)[0]
+
+        ours = S.node_indexer_create(ref, prob, meshes, m2l, vindex, nets, lookup=lookup)
+        assert calls == [sum(len(n.connections) for n in nets)]           # ONE batched call
+        assert ours.internal_node_count == stock.internal_node_count
+        assert ours.node_to_global_index == stock.node_to_global_index    # same NodeID objects, same indices
+        assert ours.extra_source_to_global_index == stock.extra_source_to_global_index
+        assert "_construct_kdtrees" in ref.NodeIndexer.__dict__            # the reference class is restored
+        again = ref.NodeIndexer.create(prob, meshes, m2l, vindex, nets)
+        assert again.node_to_global_index == stock.node_to_global_index
