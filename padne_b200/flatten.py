@@ -16,17 +16,29 @@ from __future__ import annotations
 
 import numpy as np
 
+from . import halfedge
 from .flat import (FlatSystem, KIND_CURRENT, KIND_REGULATOR, KIND_RESISTOR, KIND_VOLTAGE)
 
 
 def mesh_to_arrays(msh):
-    """``(xy [n,2] f64, tri [m,3] i32)`` of one mesh, triangles in ``mesh.faces`` order."""
+    """``(xy [n,2] f64, tri [m,3] i32)`` of one mesh, triangles in ``mesh.faces`` order.
+
+    Three sources, cheapest first: arrays the object carries (``.xy`` / ``.tri``), arrays remembered
+    for this mesh by :mod:`padne_b200.halfedge` (meshes built by ``mesh_from_triangle_soup``, or walked
+    once already), and the walk over the reference's object graph, which is then remembered."""
     if hasattr(msh, "xy") and hasattr(msh, "tri"):
         return (np.ascontiguousarray(msh.xy, np.float64).reshape(-1, 2),
                 np.ascontiguousarray(msh.tri, np.int32).reshape(-1, 3))
-    xy = np.array([(v.p.x, v.p.y) for v in msh.vertices], dtype=np.float64).reshape(-1, 2)
+    hit = halfedge.known_arrays(msh)
+    if hit is not None:
+        return hit
+    xy = np.array([(p.x, p.y) for p in [v.p for v in msh.vertices]], dtype=np.float64).reshape(-1, 2)
     tri = np.array([[int(e.origin.i) for e in f.edges] for f in msh.faces],
                    dtype=np.int32).reshape(-1, 3)
+    try:
+        halfedge.register_arrays(msh, xy, tri)
+    except TypeError:                      # a duck-typed mesh that cannot be weakly referenced
+        pass
     return xy, tri
 
 

@@ -32,7 +32,7 @@ from typing import Optional
 import numpy as np
 import scipy.sparse
 
-from . import capi
+from . import capi, halfedge
 from .flat import FlatSystem, OP_ADD, OP_SET
 from .flatten import flatten_elements, flatten_system, mesh_to_arrays
 from .stamps import build_stamps
@@ -301,7 +301,8 @@ def node_indexer_create(ref, prob, meshes, mesh_index_to_layer_index, vindex, fi
         lookup = (ctx or capi.default_context(OPTIONS.device)).nearest_vertex
     conns = [c for net in filtered_networks for c in net.connections]
     v_off = np.concatenate([[0], np.cumsum([len(m.vertices) for m in meshes])]).astype(np.int64)
-    xy = np.array([(v.p.x, v.p.y) for m in meshes for v in m.vertices], np.float64).reshape(-1, 2)
+    xy = (np.concatenate([mesh_to_arrays(m)[0] for m in meshes]) if len(meshes)
+          else np.zeros((0, 2)))                             # one walk per mesh, shared with the assembly (row F2)
     q_xy = np.array([(c.point.x, c.point.y) for c in conns], np.float64).reshape(-1, 2)
     q_layer = np.array([prob.layers.index(c.layer) for c in conns], np.int32)
     idx = lookup(v_off, np.asarray(mesh_index_to_layer_index, np.int32), xy, q_xy, q_layer) if len(conns) else []
@@ -366,9 +367,11 @@ def solve(prob, mesher_config=None):
     log.info("Constructing connectivity graph and finding connected layers")
     strtrees, _, connected = ref.compute_connectivity(prob)
     log.info("Meshing the connected components")
-    meshes, m2l = ref.generate_meshes_for_problem(prob, mesher, connected, strtrees)
+    with halfedge.fast_triangle_soup(ref.mesh):              # row F2: the mesher's soup -> Mesh objects + flat arrays
+        meshes, m2l = ref.generate_meshes_for_problem(prob, mesher, connected, strtrees)
     log.info("Meshing the disconnected components")
-    disconnected = ref.generate_disconnected_meshes(prob, connected)
+    with halfedge.fast_triangle_soup(ref.mesh):
+        disconnected = ref.generate_disconnected_meshes(prob, connected)
     log.info("Processing lumped element networks")
     filtered = ref.filter_dead_networks(prob, strtrees, connected)
     log.info(f"Filtered networks: {len(filtered)}/{len(prob.networks)}")
