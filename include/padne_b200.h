@@ -187,6 +187,23 @@ int pdn_nearest_vertex(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off /*[n_m
                        const double *q_xy /*[n_q,2]*/, const int32_t *q_layer /*[n_q]*/,
                        int64_t *out_index /*[n_q]*/, double *out_d2 /*[n_q] or NULL*/, int on_device);
 
+/* ---- next row F4: the text of a ParaView .vtu piece from flat arrays (host only: the output is a file) ----
+ * Replaces the per-vertex / per-face object walks and string joins of padne/paraview.py:109-231
+ * (create_point_data, create_points, _extract_triangle_connectivity, create_cells, create_piece).
+ * Unlike the functions above these return a BYTE COUNT (>= 0) or a negated status code (< 0), need no
+ * pdn_ctx and no GPU, and take host pointers only.
+ *
+ * pdn_format_f64: " ".join(str(v) for v in x) (padne/paraview.py:91) -- CPython's float repr, byte for byte.
+ *   cap must be >= 25 * n.
+ * pdn_vtu_piece: the <Piece> element of one mesh exactly as lxml pretty-prints it inside
+ *   VTKFile/UnstructuredGrid (padne/paraview.py:276-287): PointData "voltage" = voltage[0..n_v), Points =
+ *   (x, -y, 0.0) per vertex, Cells = tri in mesh.faces order / offsets 3(i+1) / types 5.
+ *   cap must be >= pdn_vtu_piece_bound(n_v, n_t); a triangle index outside [0, n_v) gives -PDN_EINVAL. */
+int64_t pdn_format_f64(const double *x, int64_t n, char *out, int64_t cap);
+int64_t pdn_vtu_piece_bound(int64_t n_v, int64_t n_t);
+int64_t pdn_vtu_piece(int64_t n_v, const double *xy /*[n_v,2]*/, const double *voltage /*[n_v]*/, int64_t n_t,
+                      const int32_t *tri /*[n_t,3]*/, char *out, int64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -161,3 +161,39 @@ def nearest_vertex(v_off, mesh_layer, xy, q_xy, q_layer):
             out[q] = idx[k]
             d2[q] = d[k]
     return out, d2
+
+
+# -- row F4: the reference's .vtu element tree, restated over arrays (pure Python, small cases) ------------
+def vtu_piece_tree(xy, tri, values):
+    """``[tag, [[attr, value], ...], text, [children]]`` of one ``<Piece>``: ``create_piece``
+    ``padne/paraview.py:209-231`` with its children ``create_point_data`` (``:109-126``), ``create_points``
+    (``:129-146``, y negated, z = 0.0) and ``create_cells`` (``:184-206``); every payload is
+    ``" ".join(str(value) ...)`` over Python floats / ints like ``create_data_array`` (``:62-93``)."""
+    xy = [(float(x), float(y)) for x, y in np.asarray(xy, np.float64).reshape(-1, 2)]
+    tri = [tuple(int(i) for i in t) for t in np.asarray(tri).reshape(-1, 3)]
+    values = [float(x) for x in np.asarray(values, np.float64).reshape(-1)]
+
+    def data_array(data_type, items, name=None, n_comp=None):
+        attrs = [["type", data_type], ["format", "ascii"]]
+        if name is not None:
+            attrs.append(["Name", name])
+        if n_comp is not None:
+            attrs.append(["NumberOfComponents", str(n_comp)])
+        return ["DataArray", attrs, " ".join(str(v) for v in items), []]
+
+    coords = []
+    for x, y in xy:
+        coords.extend([x, -y, 0.0])
+    conn = [i for t in tri for i in t]
+    return ["Piece", [["NumberOfPoints", str(len(xy))], ["NumberOfCells", str(len(tri))]], None, [
+        ["PointData", [["Scalars", "voltage"]], None, [data_array("Float64", values, name="voltage")]],
+        ["Points", [], None, [data_array("Float64", coords, n_comp=3)]],
+        ["Cells", [], None, [data_array("Int32", conn, name="connectivity"),
+                             data_array("Int32", [3 * (i + 1) for i in range(len(tri))], name="offsets"),
+                             data_array("UInt8", [5] * len(tri), name="types")]]]]
+
+
+def vtu_file_tree(pieces):
+    """One layer document (``create_vtk_root`` ``padne/paraview.py:96-106`` + ``export_solution`` ``:270-281``)."""
+    return ["VTKFile", [["type", "UnstructuredGrid"], ["version", "0.1"], ["byte_order", "LittleEndian"]], None,
+            [["UnstructuredGrid", [], None, [vtu_piece_tree(*p) for p in pieces]]]]

@@ -26,6 +26,7 @@ UNITS = {
     "pdn_assemble.cu": ["-fmad=false"],
     "pdn_solve.cu": [],
     "pdn_multi.cu": [],
+    "pdn_vtu.cpp": [],          # host only (row F4); nvcc hands it to g++
 }
 
 
@@ -64,7 +65,7 @@ def _build(LIB: str, verbose: bool, extra: list[str], tag: str) -> str:
     objs = []
     procs = []
     for unit in _sources():
-        obj = os.path.join(LIBDIR, unit.replace(".cu", f"{tag}.o"))
+        obj = os.path.join(LIBDIR, os.path.splitext(unit)[0] + f"{tag}.o")
         cmd = [nvcc, *ARCH, *COMMON, *UNITS[unit], *extra, "-c", os.path.join(CSRC, unit), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")

@@ -27,7 +27,8 @@ METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 SYMBOLS = ("pdn_create", "pdn_destroy", "pdn_strerror", "pdn_last_error", "pdn_launch_count",
            "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_get_csr", "pdn_get_shape",
            "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density",
-           "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info", "pdn_nearest_vertex")
+           "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info", "pdn_nearest_vertex",
+           "pdn_format_f64", "pdn_vtu_piece_bound", "pdn_vtu_piece")
 
 
 class SingularSystemError(RuntimeError):
@@ -103,6 +104,12 @@ def load_library(path: str | None = None):
     lib.pdn_bench_spmv.argtypes = [P, I32, ctypes.c_int, ctypes.POINTER(D)]
     lib.pdn_power_density.argtypes = [P, I64, P, P, I64, P, D, P, ctypes.c_int]
     lib.pdn_nearest_vertex.argtypes = [P, I32, P, P, P, I64, P, P, P, P, ctypes.c_int]
+    lib.pdn_format_f64.argtypes = [P, I64, P, I64]
+    lib.pdn_format_f64.restype = I64
+    lib.pdn_vtu_piece_bound.argtypes = [I64, I64]
+    lib.pdn_vtu_piece_bound.restype = I64
+    lib.pdn_vtu_piece.argtypes = [I64, P, P, I64, P, P, I64]
+    lib.pdn_vtu_piece.restype = I64
     lib.pdn_comm_unique_id.argtypes = [P]
     lib.pdn_comm_init.argtypes = [P, ctypes.c_int, ctypes.c_int, P]
     lib.pdn_comm_destroy.argtypes = [P]
@@ -359,6 +366,33 @@ class Context:
                                                  q_xy.shape[0], _ptr(q_xy), _ptr(q_layer), _ptr(out),
                                                  _ptr(d2) if return_d2 else None, 0), "nearest_vertex")
         return (out, d2) if return_d2 else out
+
+
+# -- row F4: host-only text formatting (no context, no GPU) -------------------------------------------
+def format_f64(x) -> bytes:
+    """``" ".join(str(v) for v in x)`` for a float64 array (``padne/paraview.py:91``), CPython's repr."""
+    lib = load_library()
+    x = _np(x, np.float64).reshape(-1)
+    buf = np.empty(max(1, 25 * x.shape[0]), np.uint8)
+    n = lib.pdn_format_f64(_ptr(x), x.shape[0], _ptr(buf), buf.shape[0])
+    if n < 0:
+        _raise(lib, None, int(-n), "format_f64")
+    return buf[:n].tobytes()
+
+
+def vtu_piece(xy, tri, voltage) -> np.ndarray:
+    """The ``<Piece>`` element of one mesh (``padne/paraview.py:209-231``) as a uint8 array of XML text."""
+    lib = load_library()
+    xy = _np(xy, np.float64).reshape(-1, 2)
+    tri = _np(tri, np.int32).reshape(-1, 3)
+    voltage = _np(voltage, np.float64).reshape(-1)
+    if voltage.shape[0] != xy.shape[0]:
+        raise ValueError("vtu_piece: one voltage per vertex")
+    buf = np.empty(lib.pdn_vtu_piece_bound(xy.shape[0], tri.shape[0]), np.uint8)
+    n = lib.pdn_vtu_piece(xy.shape[0], _ptr(xy), _ptr(voltage), tri.shape[0], _ptr(tri), _ptr(buf), buf.shape[0])
+    if n < 0:
+        _raise(lib, None, int(-n), "vtu_piece")
+    return buf[:n]
 
 
 _default_ctx: dict[int, Context] = {}
