@@ -185,7 +185,16 @@ def mesh_from_triangle_soup(mesh_mod, points, triangles, mesh_cls=None):
     """``Mesh.from_triangle_soup(points, triangles)`` (``padne/mesh.py:302-378``) built from
     :func:`soup_topology`.  ``mesh_mod`` is the reference's ``padne.mesh`` module; ``points`` is a list of
     its ``Point`` objects (kept, not copied, like the reference) or an ``[n,2]`` array."""
-    mesh_cls = mesh_cls or mesh_mod.Mesh
+    gc_was_on = gc.isenabled()
+    gc.disable()    # ~9 live objects per vertex are created here: generational scans of them only cost time
+    try:
+        return _mesh_from_triangle_soup(mesh_mod, points, triangles, mesh_cls or mesh_mod.Mesh)
+    finally:
+        if gc_was_on:
+            gc.enable()
+
+
+def _mesh_from_triangle_soup(mesh_mod, points, triangles, mesh_cls):
     original = mesh_cls.__dict__.get("_pdn_original_from_triangle_soup")
     if isinstance(points, np.ndarray):
         xy = np.ascontiguousarray(points, np.float64).reshape(-1, 2)
@@ -195,21 +204,15 @@ def mesh_from_triangle_soup(mesh_mod, points, triangles, mesh_cls=None):
         points = list(points)
         xy = np.array([(p.x, p.y) for p in points], np.float64).reshape(-1, 2)
     triangles = list(triangles) if not isinstance(triangles, np.ndarray) else triangles
-    for t in (triangles if not isinstance(triangles, np.ndarray) else ()):
-        assert len(t) == 3                                            # mesh.py:311
+    if not isinstance(triangles, np.ndarray):
+        assert all(len(t) == 3 for t in triangles)                   # mesh.py:311
     try:
         topo = soup_topology(len(points), triangles if len(triangles) else np.zeros((0, 3), np.int64))
     except IrregularSoup:
         build = original.__func__ if original is not None else mesh_cls.from_triangle_soup.__func__
         return build(mesh_cls, points, triangles)
     msh = mesh_cls()
-    gc_was_on = gc.isenabled()
-    gc.disable()                    # ~9 objects per vertex, all reachable: generational scans only cost time
-    try:
-        vertices, hedges, faces, loops = _instantiate(mesh_mod, points, topo)
-    finally:
-        if gc_was_on:
-            gc.enable()
+    vertices, hedges, faces, loops = _instantiate(mesh_mod, points, topo)
     _fill_store(msh.vertices, vertices)
     _fill_store(msh.halfedges, hedges)
     _fill_store(msh.faces, faces)
