@@ -142,3 +142,26 @@ def test_miniref_flow_gives_the_reference_voltages(name):
         for za, zb, pa, pb in zip(la.potentials, lb.potentials, la.power_densities, lb.power_densities):
             np.testing.assert_allclose(za.values, zb.values, rtol=1e-9, atol=1e-12)
             np.testing.assert_allclose(pa.values, pb.values, rtol=1e-6, atol=1e-18)
+
+
+def test_laplace_operator_and_power_density_seams_on_reference_meshes():
+    """``laplace_operator(mesh)`` (``padne/solver.py:171``) and ``compute_power_density`` (``:728``) called the way
+    the reference's tests and benchmarks call them, on the reference's ``Mesh`` / ``ZeroForm``."""
+    problem, mesh, solver = refload.load_reference()
+    xy, tri, _ = synth.grid_layer(9, 7, 0.4, seed=5, jitter=0.25)
+    msh = mesh.Mesh.from_triangle_soup([mesh.Point(float(x), float(y)) for x, y in xy],
+                                       [tuple(int(i) for i in t) for t in tri])
+    want = solver.laplace_operator(msh).tocsr()
+    want.sort_indices()
+    got = S.laplace_operator(msh, OracleContext())
+    assert got.shape == want.shape and type(got).__name__ == "coo_matrix"
+    g = got.tocsr()
+    g.sort_indices()
+    assert np.array_equal(g.indptr, want.indptr) and np.array_equal(g.indices, want.indices)
+    assert np.array_equal(g.data, want.data)
+    zf = mesh.ZeroForm(msh)
+    zf.values[:] = np.random.default_rng(0).random(len(xy))
+    pd_want = solver.compute_power_density(zf, 2.0)
+    pd_got = S.compute_power_density(zf, 2.0, OracleContext())
+    assert type(pd_got) is mesh.TwoForm and pd_got.mesh is msh
+    np.testing.assert_allclose(pd_got.values, pd_want.values, rtol=1e-12, atol=0)
