@@ -123,19 +123,23 @@ char *join_items(char *p, int64_t n, int width, Item item) {
     }
     int64_t per = (n + T - 1) / T;
     std::vector<char *> ends(T, nullptr);
+    auto chunk = [=, &ends](int k) {
+        int64_t lo = std::min<int64_t>(n, k * per), hi = std::min<int64_t>(n, lo + per);
+        char *q = p + lo * width;
+        for (int64_t i = lo; i < hi; ++i) {
+            q = item(q, i);
+            *q++ = ' ';
+        }
+        ends[k] = q;
+    };
     std::vector<std::thread> pool;
     pool.reserve(T);
-    for (int k = 0; k < T; ++k) {
-        pool.emplace_back([=, &ends] {
-            int64_t lo = std::min<int64_t>(n, k * per), hi = std::min<int64_t>(n, lo + per);
-            char *q = p + lo * width;
-            for (int64_t i = lo; i < hi; ++i) {
-                q = item(q, i);
-                *q++ = ' ';
-            }
-            ends[k] = q;
-        });
+    int started = 0;
+    try {
+        for (; started < T - 1; ++started) pool.emplace_back(chunk, started);
+    } catch (...) {   // no more threads to be had: the caller's thread takes the chunks that are left
     }
+    for (int k = started; k < T; ++k) chunk(k);
     for (auto &t : pool) t.join();
     char *w = p;
     for (int k = 0; k < T; ++k) {
