@@ -165,3 +165,14 @@ def test_laplace_operator_and_power_density_seams_on_reference_meshes():
     pd_got = S.compute_power_density(zf, 2.0, OracleContext())
     assert type(pd_got) is mesh.TwoForm and pd_got.mesh is msh
     np.testing.assert_allclose(pd_got.values, pd_want.values, rtol=1e-12, atol=0)
+
+
+# ---- known answers (no reference needed: stand-in classes + the oracle behind the context) ---------------------
+def test_linear_rectangle_known_answer():
+    import analytic_cases
+    analytic_cases.check_linear_rectangle(OracleContext())
+
+
+def test_superposition_principle():
+    import analytic_cases
+    analytic_cases.check_superposition(OracleContext())

@@ -9,6 +9,7 @@ values of the assembled matrix bit-exact.  Runs last (file name) because it need
 import numpy as np
 import pytest
 
+import analytic_cases
 import miniref
 from oracle_context import OracleContext
 from padne_b200 import paraview
@@ -56,3 +57,11 @@ def test_assemble_system_object_form_is_bit_exact(ctx):
     Lo, ro = S.assemble_system(prob, meshes, m2l, vindex, nets, nidx, OracleContext())
     assert np.array_equal(L.indptr, Lo.indptr) and np.array_equal(L.indices, Lo.indices)
     assert np.array_equal(L.data, Lo.data) and np.array_equal(r, ro)
+
+
+def test_linear_rectangle_known_answer_on_the_gpu(ctx):
+    analytic_cases.check_linear_rectangle(ctx)              # tests/test_solver.py:461-595 of the reference
+
+
+def test_superposition_principle_on_the_gpu(ctx):
+    analytic_cases.check_superposition(ctx)                 # tests/test_solver.py:1449-1564 of the reference
