@@ -33,7 +33,7 @@ import numpy as np
 import scipy.sparse
 
 from . import capi, halfedge
-from .flat import FlatSystem, OP_ADD, OP_SET
+from .flat import FlatSystem, OP_SET
 from .flatten import flatten_elements, flatten_system, mesh_to_arrays
 from .stamps import build_stamps
 

@@ -7,7 +7,6 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np  # noqa: E402
 
 from bench import make_board  # noqa: E402
 from padne_b200 import capi  # noqa: E402

@@ -12,7 +12,6 @@ reference: ``set`` iteration order), which permutes unknowns beyond the vertices
 Use: ``prob, meshes, m2l = synth.to_reference_objects(board, miniref, miniref, miniref)``; ``ref=miniref.solver``.
 """
 import types
-import warnings
 from dataclasses import dataclass, field
 
 import numpy as np
