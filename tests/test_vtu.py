@@ -58,6 +58,20 @@ def test_format_matches_cpython_repr_on_random_bit_patterns(n):
         (" " + " ".join(map(repr, b[500:].tolist())) if n > 500 else "")
 
 
+def test_format_around_every_power_of_ten_and_two():
+    """The notation switches at 1e-4 and 1e16 and the digit count changes at every power of ten: the values on
+    both sides of each, and of each power of two (where the spacing of doubles changes), subnormals included."""
+    xs = []
+    for e in range(-324, 309):
+        x = float(f"1e{e}")
+        xs += [np.nextafter(x, 0.0), x, np.nextafter(x, np.inf)]
+    for e in range(-1074, 1024):
+        x = float(np.ldexp(1.0, e))
+        xs += [np.nextafter(x, 0.0), x, np.nextafter(x, np.inf)]
+    xs = np.array(xs + [-x for x in xs], np.float64)
+    assert capi.format_f64(xs).decode() == " ".join(map(repr, xs.tolist()))
+
+
 def test_thread_count_does_not_change_the_text(monkeypatch):
     a = np.random.default_rng(5).normal(size=150_001) * 1e3
     want = " ".join(map(repr, a.tolist())).encode()
