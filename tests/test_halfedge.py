@@ -48,6 +48,16 @@ def _soups():
     perm = rng.permutation(tri.shape[0])
     rot = np.array([np.roll(t, int(k)) for t, k in zip(tri[perm], rng.integers(0, 3, tri.shape[0]))])
     out.append(("grid_shuffled", xy, rot.astype(np.int64)))
+    # unstructured clouds (what a quality mesher emits: valences 3..10, ragged boundary), one with a hole
+    from scipy.spatial import Delaunay
+    for name, n_pts, hole in (("delaunay_400", 400, 0.0), ("delaunay_annulus_900", 900, 0.28)):
+        pts = np.random.default_rng(n_pts).random((n_pts, 2))
+        t = Delaunay(pts).simplices.astype(np.int64)
+        a, b, c = pts[t[:, 0]], pts[t[:, 1]], pts[t[:, 2]]
+        flip = (b[:, 0] - a[:, 0]) * (c[:, 1] - a[:, 1]) - (b[:, 1] - a[:, 1]) * (c[:, 0] - a[:, 0]) < 0
+        t[flip] = t[flip][:, (0, 2, 1)]                                   # all counter-clockwise
+        keep = np.linalg.norm((a + b + c) / 3 - 0.5, axis=1) >= hole
+        out.append((name, pts, t[keep]))
     return out
 
 
