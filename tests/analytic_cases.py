@@ -55,3 +55,48 @@ def check_superposition(ctx):
     scale = np.max(np.abs(v_full))
     assert scale > 0.1
     assert np.max(np.abs(v_full - (v_volt + v_amp))) <= 1e-6 * scale
+
+
+def delaunay_board(n_pts=1500, seed=0, n_links=6):
+    """Two layers of UNSTRUCTURED triangles -- Delaunay of a jittered point set, so no slivers but vertex valences
+    4..10 and irregular orbits like a quality mesher's output (``synth`` only makes valence-6 grids) -- one layer
+    with a ragged hole, tied by resistors placed on the highest-valence vertices (rows longer than 10 entries),
+    with one voltage and one current source."""
+    from scipy.spatial import Delaunay, cKDTree
+    rng = np.random.default_rng(seed)
+    b = synth.SynthBoard(name=f"delaunay_{n_pts}_{seed}")
+    m = max(8, int(round(np.sqrt(n_pts))))
+    pitch = 10.0 / (m - 1)
+    clouds, valences = [], []
+    for layer, hole in enumerate((0.0, 1.6)):
+        ii, jj = np.meshgrid(np.arange(m), np.arange(m), indexing="ij")
+        jit = (rng.random((m, m, 2)) - 0.5) * 0.8 * pitch
+        jit[0, :, 0] = jit[-1, :, 0] = 0.0                                     # the outline stays the square
+        jit[:, 0, 1] = jit[:, -1, 1] = 0.0
+        pts = (np.stack([ii, jj], -1) * pitch + jit).reshape(-1, 2)
+        pts = pts[np.linalg.norm(pts - 5.0, axis=1) >= hole]
+        t = Delaunay(pts).simplices.astype(np.int64)
+        a, bb, c = pts[t[:, 0]], pts[t[:, 1]], pts[t[:, 2]]
+        area2 = (bb[:, 0] - a[:, 0]) * (c[:, 1] - a[:, 1]) - (bb[:, 1] - a[:, 1]) * (c[:, 0] - a[:, 0])
+        t[area2 < 0] = t[area2 < 0][:, (0, 2, 1)]                              # all counter-clockwise
+        t = t[np.linalg.norm((a + bb + c) / 3 - 5.0, axis=1) >= 0.8 * hole]    # Delaunay fills the hole: reopen it
+        used = np.unique(t)                                                    # drop vertices no triangle uses
+        remap = np.full(len(pts), -1, np.int64)
+        remap[used] = np.arange(used.size)
+        t = remap[t]
+        b.add_mesh(b.add_layer(f"L{layer}.Cu", 2.0 + layer), pts[used], t.astype(np.int32))
+        clouds.append(pts[used])
+        valences.append(np.bincount(t.reshape(-1), minlength=used.size))
+    off = b.v_off
+    trees = [cKDTree(c) for c in clouds]
+
+    def at(layer, x, y):
+        return int(off[layer] + trees[layer].query((x, y))[1])
+
+    busiest = np.argsort(-valences[0], kind="stable")[:n_links]               # resistors between the layers
+    for k, v0 in enumerate(busiest.tolist()):
+        x, y = clouds[0][v0]
+        b.add_resistors([int(off[0] + v0)], [at(1, x, y)], 1e-3 * (1 + k))
+    b.add_voltage_source(at(0, 0.5, 5.0), at(0, 9.5, 5.0), 1.25)
+    b.add_current_source(at(1, 5.0, 9.5), at(1, 5.0, 0.5), 0.7)
+    return b

@@ -24,6 +24,7 @@ BOARDS = {
     "2layer": lambda: synth.board_2layer(16, n_via=2, size_mm=8.0, seed=2),
     "4layer_regulator": lambda: synth.board_4layer_regulator(18, n_via=2, size_mm=8.0, seed=4),
     "8layer": lambda: synth.board_8layer(12, n_via=1, size_mm=6.0, seed=6),
+    "delaunay": lambda: __import__("analytic_cases").delaunay_board(700, seed=1),      # unstructured triangles
 }
 
 
@@ -65,10 +66,11 @@ def test_solve_meshed_matches_the_reference_pipeline(name):
     pickle.loads(pickle.dumps(got))                                               # the .padne format, cli.py:223-224
 
 
-def test_assemble_system_equals_the_reference_matrix():
+@pytest.mark.parametrize("name", ["4layer_regulator", "delaunay"])
+def test_assemble_system_equals_the_reference_matrix(name):
     problem, mesh, solver = refload.load_reference()
     import shapely.geometry as geometry
-    prob, meshes, m2l = synth.to_reference_objects(BOARDS["4layer_regulator"](), problem, mesh, geometry)
+    prob, meshes, m2l = synth.to_reference_objects(BOARDS[name](), problem, mesh, geometry)
     vindex = solver.VertexIndexer.create(meshes)
     filtered = list(prob.networks)
     nidx = solver.NodeIndexer.create(prob, meshes, m2l, vindex, filtered)

@@ -23,6 +23,7 @@ BOARDS = {
     "2layer": lambda: synth.board_2layer(60, n_via=4, size_mm=30.0, seed=8),
     "4layer_regulator": lambda: synth.board_4layer_regulator(26, n_via=2, size_mm=12.0, seed=4),
     "8layer": lambda: synth.board_8layer(16, n_via=1, size_mm=8.0, seed=6),
+    "delaunay": lambda: analytic_cases.delaunay_board(1500, seed=0),     # unstructured: valences 3..12
 }
 
 
@@ -65,3 +66,27 @@ def test_linear_rectangle_known_answer_on_the_gpu(ctx):
 
 def test_superposition_principle_on_the_gpu(ctx):
     analytic_cases.check_superposition(ctx)                 # tests/test_solver.py:1449-1564 of the reference
+
+
+@pytest.mark.parametrize("n_pts", [1500, 30000])
+def test_unstructured_triangles_assembly_bit_exact_and_solve(ctx, n_pts):
+    """Delaunay clouds instead of the valence-6 grids of ``synth``: vertex orbits of 3..12 triangles, ragged
+    boundaries, a hole, rows longer than the SpMV's shared-memory slice width (its direct-load path)."""
+    import scipy.sparse
+    from oracle import oracle
+    from padne_b200.stamps import build_stamps
+    fs = analytic_cases.delaunay_board(n_pts, seed=n_pts).to_flat()
+    s_row, s_col, s_val, s_op, rhs = build_stamps(fs)
+    ctx.assemble(fs.v_off, fs.xy, fs.t_off, fs.tri, fs.conductance, fs.N, s_row, s_col, s_val, s_op)
+    indptr, indices, data = ctx.get_csr()
+    o_indptr, o_indices, o_data = oracle.assemble(fs, (s_row, s_col, s_val, s_op))
+    assert np.array_equal(indptr, o_indptr) and np.array_equal(indices, o_indices)
+    assert np.array_equal(data, o_data)                                            # values bit-exact
+    assert np.diff(indptr)[:fs.n_nodes].max() > 10                                 # wider than a TMA slice slot
+    v, info = ctx.solve(rhs, n_nodes=fs.n_nodes)
+    v_ref, _, _ = oracle.solve(o_indptr, o_indices, o_data, rhs)                   # the reference's spsolve call
+    assert info.rel_residual <= 1e-10
+    scale = np.max(np.abs(v_ref[:fs.n_nodes]))
+    assert np.max(np.abs(v[:fs.n_nodes] - v_ref[:fs.n_nodes])) <= 1e-6 * scale
+    L = scipy.sparse.csr_matrix((data, indices, indptr), shape=(fs.N, fs.N))
+    assert np.linalg.norm(L @ v - rhs) <= 1e-8 * max(1.0, np.linalg.norm(rhs))
