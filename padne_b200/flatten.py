@@ -14,6 +14,8 @@ Duck-typed on the reference's own classes so that the caller keeps using ``padne
 """
 from __future__ import annotations
 
+import operator
+
 import numpy as np
 
 from . import halfedge
@@ -33,13 +35,30 @@ def mesh_to_arrays(msh):
     if hit is not None:
         return hit
     xy = np.array([(p.x, p.y) for p in [v.p for v in msh.vertices]], dtype=np.float64).reshape(-1, 2)
-    tri = np.array([[int(e.origin.i) for e in f.edges] for f in msh.faces],
-                   dtype=np.int32).reshape(-1, 3)
+    tri = _walk_faces(msh)
     try:
         halfedge.register_arrays(msh, xy, tri)
     except TypeError:                      # a duck-typed mesh that cannot be weakly referenced
         pass
     return xy, tri
+
+
+def _walk_faces(msh) -> np.ndarray:
+    """``[[e.origin.i for e in f.edges] for f in mesh.faces]`` (``padne/mesh.py:148-160``).  On the reference's
+    half-edge objects the three corners are read by pointer (``face.edge``, ``.next``, ``.next.next``) instead of
+    through the ``edges`` generator; any face that is not a closed triangle takes the generic walk."""
+    try:
+        nxt, corner = operator.attrgetter("next"), operator.attrgetter("origin.i")
+        e0 = [f.edge for f in msh.faces]
+        e1 = list(map(nxt, e0))
+        e2 = list(map(nxt, e1))
+        if all(map(operator.is_, map(nxt, e2), e0)):
+            n = len(e0)
+            return np.stack([np.fromiter(map(corner, e), np.int64, n) for e in (e0, e1, e2)],
+                            axis=1).astype(np.int32).reshape(-1, 3)
+    except AttributeError:                 # a duck-typed mesh that only offers ``face.edges``
+        pass
+    return np.array([[int(e.origin.i) for e in f.edges] for f in msh.faces], dtype=np.int32).reshape(-1, 3)
 
 
 def find_best_ground_node_index(prob, node_indexer) -> int:
