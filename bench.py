@@ -141,28 +141,141 @@ def cpu_port_dofs(config: str, n_sample: int, repeats: int = 1):
     return fs.N / best, fs.N, t_asm, t_solve
 
 
+def cpu_reference_dofs(config: str, n_sample: int, repeats: int = 1):
+    """The reference's OWN ``assemble_system`` + ``solve_system`` (``padne/solver.py:783-812, 767-780``),
+    unmodified, on reference objects built (untimed) by its own ``Mesh.from_triangle_soup`` /
+    ``VertexIndexer`` / ``NodeIndexer``.  The modules come from ``/root/reference`` when it is mounted, else
+    from ``oracle/_ref`` (``oracle/make_ref.py``).  Returns None when neither is present."""
+    from oracle import refload
+    if not refload.reference_available():
+        return None
+    import warnings
+    from padne_b200 import synth
+    problem, mesh, solver = refload.load_reference()
+    import shapely.geometry as geometry          # the loader's stub
+    board = make_board(config, n_sample)
+    t0 = time.perf_counter()
+    prob, meshes, m2l = synth.to_reference_objects(board, problem, mesh, geometry)
+    vindex = solver.VertexIndexer.create(meshes)
+    nets = list(prob.networks)
+    nidx = solver.NodeIndexer.create(prob, meshes, m2l, vindex, nets)
+    t_prep = time.perf_counter() - t0
+    best, times = None, []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        L, r = solver.assemble_system(prob, meshes, m2l, vindex, nets, nidx)
+        t1 = time.perf_counter()
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            v, info = solver.solve_system(L, r)
+        t2 = time.perf_counter()
+        times.append(t2 - t0)
+        if best is None or t2 - t0 < best["t"]:
+            best = dict(t=t2 - t0, t_asm=t1 - t0, t_solve=t2 - t1, N=int(L.shape[0]),
+                        residual_norm=float(info.residual_norm), ground_node_current=float(info.ground_node_current))
+    best.update(dofs=best["N"] / best["t"], t_prep=t_prep, origin=refload.reference_origin(), times=times)
+    return best
+
+
+def host_cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (oracle port) on the host cores, rank 0 only."""
+    """--impl reference: the reference's own CPU path on the host cores, rank 0 only.  The reference's
+    modules (oracle/_ref or /root/reference) are timed when present, else the oracle port."""
     if rank != 0:
         return
-    n_sample = args.n or args.cpu_sample_n
+    n_sample = args.n or args.ref_sample_n
     vals = []
-    for k in range(args.warmup + args.steps):
-        dofs, N, t_asm, t_solve = cpu_port_dofs(args.config, n_sample)
-        if k >= args.warmup:
-            vals.append((dofs, t_asm + t_solve))
-    value = float(np.mean([v[0] for v in vals]))
-    ms = float(np.mean([v[1] for v in vals]) * 1e3)
-    sample = (f"{args.config} board family at grid {n_sample} ({N} DOF) per step: oracle C assembly restatement "
-              f"+ the reference's scipy.sparse.linalg.spsolve call; the reference's own Python assembly is ~100x "
-              f"slower than this port")
+    ref = cpu_reference_dofs(args.config, n_sample, repeats=args.warmup + args.steps)   # objects built once, untimed
+    if ref is not None:
+        vals = [(ref["N"] / t, t) for t in ref["times"][args.warmup:]]
+        value = float(np.mean([v[0] for v in vals]))
+        ms = float(np.mean([v[1] for v in vals]) * 1e3)
+        port_dofs, port_N, _, _ = cpu_port_dofs(args.config, n_sample)
+        sample = (f"{args.config} board family at grid {n_sample} ({ref['N']} DOF) per step: the reference's own "
+                  f"assemble_system ({ref['t_asm']:.2f} s) + solve_system ({ref['t_solve']:.2f} s), unmodified modules from "
+                  f"{ref['origin']}; Mesh.from_triangle_soup / VertexIndexer / NodeIndexer ({ref['t_prep']:.2f} s) untimed; "
+                  f"1 of {os.cpu_count()} cores ({host_cpu_model()}), the path is serial Python + SuperLU")
+        cpu = {"value": value, "unit": UNIT, "cores": 1, "kind": "reference", "sample": sample,
+               "residual_norm": ref["residual_norm"], "ground_node_current": ref["ground_node_current"],
+               "port_value": port_dofs, "port_note": "oracle C assembly restatement + scipy spsolve on the same sample"}
+        N = ref["N"]
+    else:
+        n_sample = args.n or args.cpu_sample_n
+        for k in range(args.warmup + args.steps):
+            dofs, N, t_asm, t_solve = cpu_port_dofs(args.config, n_sample)
+            if k >= args.warmup:
+                vals.append((dofs, t_asm + t_solve))
+        value = float(np.mean([v[0] for v in vals]))
+        ms = float(np.mean([v[1] for v in vals]) * 1e3)
+        sample = (f"{args.config} board family at grid {n_sample} ({N} DOF) per step: oracle C assembly restatement "
+                  f"+ the reference's scipy.sparse.linalg.spsolve call (oracle/_ref absent: run oracle/make_ref.py "
+                  f"where /root/reference is mounted)")
+        cpu = {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample}
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.config, "grid": n_sample, "dof": N},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+            "cpu_baseline": cpu,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def info_dict(info):
+    """The solver's own account of one solve, for the JSON line."""
+    return {"method": info.method, "preconditioner": info.precond, "iteration_kind": info.iteration_kind,
+            "iterations": info.iterations, "restarts": info.restarts, "stagnated": info.stagnated,
+            "n_coarse": info.n_coarse, "n_coarse_local": info.n_coarse_local, "local_level": info.local_level,
+            "t_coarse_ms": info.t_coarse_ms, "rel_residual": info.rel_residual, "residual_norm": info.residual_norm,
+            "ground_node_current": info.ground_node_current, "abs_target": info.abs_target, "floor_abs": info.floor_abs,
+            "rhs_norm": info.rhs_norm, "t_krylov_ms": info.t_krylov_ms, "t_setup_ms": info.t_setup_ms,
+            "us_per_iteration": 1e3 * info.t_krylov_ms / max(info.iterations, 1),
+            "spmv": "x-band staging" if info.spmv_kind == 1 else "tma ring", "spmv_halo_rows": info.spmv_halo,
+            "spmv_window_coverage": info.spmv_window_coverage}
+
+
+class Workload:
+    """One synthetic board on this rank: pinned host copies, device copies, and the two timed steps."""
+
+    def __init__(self, torch, capi, ctx, dev, config, n, skw):
+        from padne_b200.stamps import build_stamps
+        self.torch, self.ctx, self.config = torch, ctx, config
+        fs = make_board(config, n).to_flat()
+        s_row, s_col, s_val, s_op, rhs = build_stamps(fs)
+        host = dict(v_off=fs.v_off, xy=fs.xy, t_off=fs.t_off, tri=fs.tri, cond=fs.conductance, s_row=s_row,
+                    s_col=s_col, s_val=s_val, s_op=s_op, rhs=rhs)
+        self.fs = fs
+        self.pinned = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in host.items()}
+        self.pinned_np = {k: t.numpy() for k, t in self.pinned.items()}
+        self.devt = {k: t.to(dev) for k, t in self.pinned.items()}
+        self.v_dev = torch.empty(fs.N, dtype=torch.float64, device=dev)
+        self.v_host = torch.empty(fs.N, dtype=torch.float64).pin_memory()
+        self.v_host_np = self.v_host.numpy()
+        self.h2d = int(sum(t.numel() * t.element_size() for t in self.pinned.values()))
+        self.d2h = int(fs.N * 8)
+        self.skw = dict(skw, n_nodes=fs.n_nodes)
+
+    def step_device(self):
+        d, fs = self.devt, self.fs
+        nnz = self.ctx.assemble(d["v_off"], d["xy"], d["t_off"], d["tri"], d["cond"], fs.N, d["s_row"], d["s_col"],
+                                d["s_val"], d["s_op"])
+        _, info = self.ctx.solve(d["rhs"], out=self.v_dev, **self.skw)
+        return nnz, info
+
+    def step_host(self):
+        p, fs = self.pinned_np, self.fs
+        nnz = self.ctx.assemble(p["v_off"], p["xy"], p["t_off"], p["tri"], p["cond"], fs.N, p["s_row"], p["s_col"],
+                                p["s_val"], p["s_op"])
+        _, info = self.ctx.solve(p["rhs"], out=self.v_host_np, **self.skw)
+        return nnz, info
 
 
 def main():
@@ -174,9 +287,15 @@ def main():
     ap.add_argument("--multi", default="partitioned", choices=["partitioned", "independent"])
     ap.add_argument("--n", type=int, default=None, help="grid vertices per side (default: the config's full size)")
     ap.add_argument("--impl", default="padne_b200", choices=["padne_b200", "reference"])
-    ap.add_argument("--cpu-sample-n", type=int, default=260, help="grid size of the CPU-baseline sample")
+    ap.add_argument("--cpu-sample-n", type=int, default=260, help="grid size of the CPU-baseline sample (oracle port)")
+    ap.add_argument("--ref-sample-n", type=int, default=160,
+                    help="grid size of the sample the reference's own Python path is timed on (~5 s per step at 160)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-named-configs", action="store_true",
+                    help="skip the BASELINE configs 3 and 4 block (4layer_regulator_4M, 8layer_10M)")
+    ap.add_argument("--named-steps", type=int, default=3)
     ap.add_argument("--rtol", type=float, default=1e-10)
+    ap.add_argument("--atol", type=float, default=0.0, help="absolute bar on ||L v - r||; 0 = the reference's 1e-9, <0 = off")
     ap.add_argument("--precond", default="auto", choices=["auto", "jacobi", "two-level"])
     ap.add_argument("--n-coarse", type=int, default=0)
     args = ap.parse_args()
@@ -187,15 +306,17 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     partitioned = world > 1 and args.multi == "partitioned"
     scaling = "weak"
+    default_config = args.config is None
     if args.config is None:
         args.config = f"stack_{2 * world}layer" if partitioned else "2layer_1M"
     elif partitioned:
         scaling = "strong"
     args.scaling = scaling
     if args.config.startswith("stack_") and args.n is None:
-        # keep the bounded CPU sample at ~130k DOF whatever the number of layers
+        # keep the bounded CPU samples at the same DOF count whatever the number of layers
         layers = int(args.config.split("_")[1].replace("layer", ""))
         args.cpu_sample_n = max(40, int(args.cpu_sample_n * (2.0 / layers) ** 0.5))
+        args.ref_sample_n = max(30, int(args.ref_sample_n * (2.0 / layers) ** 0.5))
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -203,7 +324,6 @@ def main():
     import torch
     import torch.distributed as dist
     from padne_b200 import capi
-    from padne_b200.stamps import build_stamps
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
@@ -217,75 +337,56 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- the board (one per rank; seeds differ so ranks do not solve the same numbers) -------------
-    board = make_board(args.config, args.n)
-    fs = board.to_flat()
-    s_row, s_col, s_val, s_op, rhs = build_stamps(fs)
-    host = dict(v_off=fs.v_off, xy=fs.xy, t_off=fs.t_off, tri=fs.tri, cond=fs.conductance, s_row=s_row,
-                s_col=s_col, s_val=s_val, s_op=s_op, rhs=rhs)
-    pinned = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in host.items()}
-    pinned_np = {k: t.numpy() for k, t in pinned.items()}
-    devt = {k: t.to(dev) for k, t in pinned.items()}
-    v_dev = torch.empty(fs.N, dtype=torch.float64, device=dev)
-    v_host = torch.empty(fs.N, dtype=torch.float64).pin_memory()
-    v_host_np = v_host.numpy()
-    h2d = int(sum(t.numel() * t.element_size() for t in pinned.values()))
-    d2h = int(fs.N * 8)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-
     ctx = capi.Context(local_rank)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     if partitioned:
         from padne_b200 import dist as pdist
-        pdist.init_comm(ctx)                # every pdn_solve below is a collective over all ranks
+        pdist.init_comm(ctx)                # every pdn_solve on ctx is a collective over all ranks
 
     precond = {"auto": capi.PRECOND_AUTO, "jacobi": capi.PRECOND_JACOBI, "two-level": capi.PRECOND_TWOLEVEL}[args.precond]
-    skw = dict(n_nodes=fs.n_nodes, rtol=args.rtol, precond=precond, n_coarse=args.n_coarse)
+    skw = dict(rtol=args.rtol, atol=args.atol, precond=precond, n_coarse=args.n_coarse)
 
-    def step_device():
-        nnz = ctx.assemble(devt["v_off"], devt["xy"], devt["t_off"], devt["tri"], devt["cond"], fs.N,
-                           devt["s_row"], devt["s_col"], devt["s_val"], devt["s_op"])
-        _, info = ctx.solve(devt["rhs"], out=v_dev, **skw)
-        return nnz, info
-
-    def step_host():
-        p = pinned_np
-        ctx.assemble(p["v_off"], p["xy"], p["t_off"], p["tri"], p["cond"], fs.N, p["s_row"], p["s_col"],
-                     p["s_val"], p["s_op"])
-        _, info = ctx.solve(p["rhs"], out=v_host_np, **skw)
-        return info
-
-    def timed(fn, steps, warmup):
+    def timed(c, fn, steps, warmup, collective):
+        """steps timed calls of fn on context c: CUDA events on its stream, L2 flushed before each, max over ranks."""
+        stream = ext if c is ctx else torch.cuda.ExternalStream(c.stream, device=dev)
         for _ in range(warmup):
             fn()
-        barrier()
-        ms, infos = [], []
-        launches0 = ctx.launch_count
+        if collective:
+            barrier()
+        else:
+            torch.cuda.synchronize()
+        ms, outs = [], []
+        launches0 = c.launch_count
         for _ in range(steps):
             flush.zero_()                       # L2 flush between timed iterations (outside the events)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(ext)
-            infos.append(fn())
-            e1.record(ext)
+            e0.record(stream)
+            outs.append(fn())
+            e1.record(stream)
             e1.synchronize()
             ms.append(e0.elapsed_time(e1))
-        launches = ctx.launch_count - launches0
-        barrier()
+        launches = c.launch_count - launches0
         total = torch.tensor([sum(ms)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(total, op=dist.ReduceOp.MAX)
-        return float(total.item()), infos, launches
+        if collective:
+            barrier()
+            if world > 1:
+                dist.all_reduce(total, op=dist.ReduceOp.MAX)
+        return float(total.item()), outs, launches
 
+    # ---- the headline workload ---------------------------------------------------------------------
+    wl = Workload(torch, capi, ctx, dev, args.config, args.n, skw)
+    fs = wl.fs
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    t_dev_ms, infos_dev, launches = timed(step_device, args.steps, args.warmup)
+    t_dev_ms, outs_dev, launches = timed(ctx, wl.step_device, args.steps, args.warmup, True)
     clocks = sampler.stop() if rank == 0 else None
-    t_e2e_ms, infos_e2e, _ = timed(step_host, args.steps, 1)
-    nnz, info = infos_dev[-1]
+    t_e2e_ms, outs_e2e, _ = timed(ctx, wl.step_host, args.steps, 1, True)
+    nnz, info = outs_dev[-1]
 
-    # ---- dominant kernel: SpMV with fused dots, in situ --------------------------------------------
+    # ---- dominant kernel: SpMV with fused dots (and, round-2 iteration, the restriction), in situ ---------
     n_red = fs.n_nodes
     indptr_tail = ctx.get_csr()[0]
     nnz_nodes = int(indptr_tail[n_red])
@@ -305,6 +406,35 @@ def main():
     except Exception:
         pass
     achieved = alg_bytes / (spmv_ms * 1e-3) / 1e9
+
+    # ---- BASELINE configs 3 and 4, inside the same run (put them on the driver's record) ------
+    named = {}
+    if default_config and not args.no_named_configs and args.n is None:
+        del wl.devt, wl.pinned, wl.pinned_np        # ~0.4 GB per GPU back before the 10M board arrives
+        torch.cuda.empty_cache()
+        # config 4: the 8-layer 300x300 mm backplane, ~10M DOF, strong-scaled over the ranks of this run
+        w4 = Workload(torch, capi, ctx, dev, "8layer_10M", None, skw)
+        t4, o4, _ = timed(ctx, w4.step_device, args.named_steps, 2, True)
+        i4 = o4[-1][1]
+        named["8layer_10M"] = dict(info_dict(i4), dof=w4.fs.N, n_gpus=world, scaling="strong" if world > 1 else "single GPU",
+                                   steps=args.named_steps, ms_per_step=t4 / args.named_steps,
+                                   value=w4.fs.N * args.named_steps / (t4 * 1e-3), unit=UNIT,
+                                   north_star="10M DOF assembled and solved in < 1 s on 8 GPUs")
+        del w4
+        torch.cuda.empty_cache()
+        # config 3: 4 layers, via arrays, two REGULATORs (non-symmetric: BiCGSTAB), ~4M DOF, one GPU (rank 0 alone)
+        if rank == 0:
+            c3 = capi.Context(local_rank)
+            w3 = Workload(torch, capi, c3, dev, "4layer_regulator_4M", None, skw)
+            t3, o3, _ = timed(c3, w3.step_device, args.named_steps, 2, False)
+            i3 = o3[-1][1]
+            named["4layer_regulator_4M"] = dict(info_dict(i3), dof=w3.fs.N, n_gpus=1, steps=args.named_steps,
+                                                ms_per_step=t3 / args.named_steps,
+                                                value=w3.fs.N * args.named_steps / (t3 * 1e-3), unit=UNIT)
+            del w3
+            c3.close()
+        barrier()
+
     if world > 1 and os.environ.get("PADNE_B200_PEER_STATS"):
         ctx.comm_destroy()                  # prints the per-exchange wait cycles (collective: every rank)
 
@@ -316,41 +446,53 @@ def main():
     dofs_total = fs.N * args.steps * (1 if partitioned else world)
     value = dofs_total / (t_dev_ms * 1e-3)
     e2e_value = dofs_total / (t_e2e_ms * 1e-3)
+    kernel_name = ("pdnk::sell_xs_kernel<CG2> (SELL-32-sigma SpMV, x window staged in shared memory, fused r.z, z.w, r.r "
+                   "and the restriction P^T w)" if info.iteration_kind == 2 else
+                   ("pdnk::sell_xs_kernel<CG>" if info.spmv_kind == 1 else "pdnk::sell_tma_kernel<CG>") +
+                   " (SELL-32-sigma SpMV, fused r.z, z.w, r.r)")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_dev_ms / args.steps, "higher_is_better": True,
         "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.config, "grid": args.n or "full", "dof": fs.N,
-                   "dof_per_gpu": fs.N // world if partitioned else fs.N, "nnz": int(nnz),
-                   "layers": fs.n_mesh, "elements": fs.n_elements, "method": info.method,
-                   "preconditioner": info.precond, "n_coarse": info.n_coarse, "t_coarse_ms": info.t_coarse_ms,
-                   "iterations": info.iterations, "rtol": args.rtol,
-                   "rel_residual": info.rel_residual, "residual_norm": info.residual_norm,
-                   "t_krylov_ms": info.t_krylov_ms, "t_setup_ms": info.t_setup_ms,
-                   "parallelism": ("single GPU" if world == 1 else
-                                   f"one board row-partitioned over {world} GPUs (halo, dot and coarse-residual exchanges as "
-                                   f"peer-memory stores over NVLink, NCCL for setup; assembly replicated)" if partitioned else f"{world} independent boards, one per GPU"),
-                   "l2": "256 MiB written between timed steps; per-step working set exceeds the 126 MB L2"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+        "config": dict({"workload": args.config, "grid": args.n or "full", "dof": fs.N,
+                        "dof_per_gpu": fs.N // world if partitioned else fs.N, "nnz": int(nnz),
+                        "layers": fs.n_mesh, "elements": fs.n_elements, "rtol": args.rtol,
+                        "atol": args.atol if args.atol != 0 else 1e-9}, **info_dict(info),
+                       parallelism=("single GPU" if world == 1 else
+                                    f"one board row-partitioned over {world} GPUs (one peer-memory exchange of dots + coarse "
+                                    f"sums and one halo exchange per iteration over NVLink, NCCL for setup; assembly replicated)"
+                                    if partitioned else f"{world} independent boards, one per GPU"),
+                       l2="256 MiB written between timed steps; per-step working set exceeds the 126 MB L2"),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
                 "ms_per_step": t_e2e_ms / args.steps},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "pdnk::sell_tma_kernel<CG> (SELL-32-sigma SpMV, per-warp TMA ring, fused r.z, z.w, r.r)",
+        "roofline": {"bound": "hbm", "kernel": kernel_name,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                      "ms_per_launch_in_situ": spmv_ms, "ms_per_launch_warm_l2": spmv_ms_warm,
                      "ms_per_launch_cold_l2": spmv_ms_cold,
-                     "note": "matrix + vectors of this config are close to the L2 size; in-situ timing "
-                             "interleaves the PCG vector update like a solver iteration"},
+                     "note": "algorithmic bytes = SURVEY.md 8d (12 B per stored entry + 20 B per row); in-situ timing "
+                             "interleaves the other kernels of a solver iteration, events around the SpMV only"},
     }
+    if named:
+        line["named_configs"] = named
     if not args.no_cpu_baseline:
-        t0 = time.perf_counter()
         dofs, n_cpu, t_asm, t_solve = cpu_port_dofs(args.config, args.cpu_sample_n)
-        line["cpu_baseline"] = {
-            "value": dofs, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"{args.config} board family at grid {args.cpu_sample_n} ({n_cpu} DOF): oracle C assembly "
-                      f"{t_asm:.2f} s + scipy spsolve (the reference's solver call) {t_solve:.2f} s; host has "
-                      f"{os.cpu_count()} cores, the path is serial"}
+        port_sample = (f"{args.config} board family at grid {args.cpu_sample_n} ({n_cpu} DOF): oracle C assembly "
+                       f"{t_asm:.2f} s + scipy spsolve (the reference's solver call) {t_solve:.2f} s")
+        ref = cpu_reference_dofs(args.config, args.ref_sample_n)
+        if ref is not None:
+            line["cpu_baseline"] = {
+                "value": ref["dofs"], "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": f"{args.config} board family at grid {args.ref_sample_n} ({ref['N']} DOF): the reference's own "
+                          f"assemble_system {ref['t_asm']:.2f} s + solve_system {ref['t_solve']:.2f} s (unmodified modules, "
+                          f"{ref['origin']}); 1 of {os.cpu_count()} cores ({host_cpu_model()}), the path is serial",
+                "residual_norm": ref["residual_norm"], "ground_node_current": ref["ground_node_current"],
+                "port_value": dofs, "port_sample": port_sample}
+        else:
+            line["cpu_baseline"] = {"value": dofs, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": port_sample + f"; host has {os.cpu_count()} cores, the path is serial"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -54,7 +54,7 @@ extern "C" {
 #define PDN_PRECOND_AUTO 0      /* two-level when the system came from pdn_assemble (coordinates are
                                    resident) and has >= 1024 rows, else Jacobi                          */
 #define PDN_PRECOND_NONE 1
-#define PDN_PRECOND_AMG 2       /* reserved (multilevel aggregation); pdn_solve answers PDN_EUNSUPPORTED */
+/* (2 is unassigned) */
 #define PDN_PRECOND_TWOLEVEL 3  /* Jacobi + coarse space of piecewise constants over coordinate bins (PCG
                                    and BiCGSTAB); partitioned PCG adds a rank-local level from 4 ranks  */
 #define PDN_PRECOND_JACOBI 4
@@ -62,14 +62,17 @@ extern "C" {
 typedef struct pdn_ctx pdn_ctx;
 
 typedef struct pdn_opts {
-    double rtol;        /* stop when ||b - A u||_2 <= rtol * ||b||_2 on the reduced system; 0 -> 1e-10 */
-    double atol;        /* ... or <= atol (absolute); 0 -> disabled                                 */
+    double rtol;        /* required: ||b - A u||_2 <= rtol * ||b||_2 on the reduced system; 0 -> 1e-10 */
+    double atol;        /* AND the reference's absolute bar on ||L v - r||_2 (its own test asserts < 1e-9,
+                           tests/test_solver.py:2083-2089): the loop runs on to max(atol / 4, the fp64 floor
+                           4 u amax ||u||_2); 0 -> 1e-9, < 0 -> disabled (rtol only)                     */
     int32_t max_iter;   /* 0 -> 20 * sqrt(N) + 2000                                                 */
     int32_t method;     /* PDN_METHOD_*                                                            */
     int32_t precond;    /* PDN_PRECOND_*                                                           */
     int32_t check_every;/* iterations per CUDA-graph launch between host convergence polls; 0 -> 32 */
     int64_t n_nodes;    /* voltage unknowns; <0 -> detect (trailing rows without a diagonal entry)  */
-    int32_t n_coarse;   /* target number of aggregates of the two-level preconditioner; 0 -> 1024    */
+    int32_t n_coarse;   /* target number of aggregates of the two-level preconditioner; 0 -> 1024 below
+                           200 000 rows, 1600 above; capped at 1776                                    */
     int32_t reserved;
 } pdn_opts;
 
@@ -89,6 +92,17 @@ typedef struct pdn_info {
     int32_t precond;            /* PDN_PRECOND_* actually used                                      */
     int32_t n_coarse;           /* aggregates of the coarse space (0 without one)                   */
     double t_coarse_ms;         /* part of t_setup_ms spent building and inverting the coarse matrix */
+    int32_t n_coarse_local;     /* aggregates of THIS rank's local level (partitioned PCG; 0 without one) */
+    int32_t local_level;        /* 0 not requested, 1 built on every rank, -1 requested but dropped         */
+    int32_t stagnated;          /* 1: the true residual stopped improving above the absolute target (fp64
+                                   floor) -- rtol still holds, or the call would have failed               */
+    int32_t iteration_kind;     /* 2: three-kernel PCG iteration with one reduction; 1: round-1 iteration   */
+    double abs_target;          /* absolute bar on the reduced residual the loop finally ran to             */
+    double floor_abs;           /* 4 u amax ||u||_2 (0 if it was never needed)                              */
+    double rhs_norm;            /* ||b||_2 of the reduced system                                            */
+    int32_t spmv_kind;          /* 1: x-band staging SpMV, 0: TMA-ring SpMV                                 */
+    int32_t spmv_halo;          /* rows of x staged either side of a CTA's rows                             */
+    double spmv_window_coverage;/* fraction of stored entries gathered from the shared-memory window       */
 } pdn_info;
 
 /* ---- context ------------------------------------------------------------------------------- */

@@ -2,12 +2,15 @@
 
 TEST INFRASTRUCTURE ONLY.  Nothing in ``padne_b200/`` may import this module.
 
-The reference lives at ``/root/reference`` and exists only in the build container (it is
-not present on the GPU box), so this loader is used for two things only:
+The reference lives at ``/root/reference`` in the build container.  It is not present on the GPU box;
+there the loader falls back to ``oracle/_ref/`` -- the byte-for-byte copy of the three hot-path modules
+made by ``oracle/make_ref.py`` (git-ignored, shipped with the snapshot).  Users:
 
-* ``tests/golden/make_golden.py`` -- generate the committed golden fixtures;
-* ``tests/test_oracle_vs_reference.py`` -- pin ``oracle/`` against the real reference
-  (skipped automatically when ``/root/reference`` is absent).
+* ``tests/golden/make_golden*.py`` -- generate the committed golden fixtures (build container);
+* ``tests/test_dropin.py``, ``tests/test_halfedge.py``, ``tests/test_oracle.py`` -- pin the oracle and the
+  host mirror against the real reference (skipped automatically when no reference is found);
+* ``bench.py --impl reference`` / ``cpu_baseline`` -- time the reference's own ``assemble_system`` +
+  ``solve_system`` (``padne/solver.py:783-812, 767-780``) on the host cores (``kind: "reference"``).
 
 Three stubs make ``padne/problem.py``, ``padne/mesh.py`` and ``padne/solver.py`` import
 without KiCad, shapely or the CGAL extension:
@@ -24,11 +27,26 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("PADNE_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _find_root() -> str:
+    for cand in (os.environ.get("PADNE_REFERENCE_ROOT"), "/root/reference", os.path.join(_HERE, "_ref")):
+        if cand and os.path.isfile(os.path.join(cand, "padne", "solver.py")):
+            return cand
+    return os.environ.get("PADNE_REFERENCE_ROOT", "/root/reference")
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def reference_available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "padne", "solver.py"))
+
+
+def reference_origin() -> str:
+    """Where the loaded modules come from: the mounted reference or the shipped copy of its files."""
+    return "oracle/_ref (copy made by oracle/make_ref.py)" if REFERENCE_ROOT.startswith(_HERE) else REFERENCE_ROOT
 
 
 class _StubPoint:

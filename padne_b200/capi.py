@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "_lib", "libpadne_b200.so")
 PDN_OK, PDN_EINVAL, PDN_EDEGENERATE, PDN_ESINGULAR, PDN_ENOTCONVERGED = 0, 1, 2, 3, 4
 PDN_ECUDA, PDN_EUNSUPPORTED, PDN_ENONMANIFOLD, PDN_ENOMEM, PDN_ENOSYSTEM = 5, 6, 7, 8, 9
 METHOD_AUTO, METHOD_PCG, METHOD_BICGSTAB = 0, 1, 2
-PRECOND_AUTO, PRECOND_NONE, PRECOND_AMG, PRECOND_TWOLEVEL, PRECOND_JACOBI = 0, 1, 2, 3, 4
+PRECOND_AUTO, PRECOND_NONE, PRECOND_TWOLEVEL, PRECOND_JACOBI = 0, 1, 3, 4
 PRECOND_NAMES = {PRECOND_NONE: "none", PRECOND_TWOLEVEL: "two-level", PRECOND_JACOBI: "jacobi"}
 METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 
@@ -51,7 +51,11 @@ class PdnInfo(ctypes.Structure):
                 ("residual_norm", ctypes.c_double), ("ground_node_current", ctypes.c_double),
                 ("t_setup_ms", ctypes.c_double), ("t_krylov_ms", ctypes.c_double),
                 ("t_total_ms", ctypes.c_double), ("spmv_ms", ctypes.c_double),
-                ("precond", ctypes.c_int32), ("n_coarse", ctypes.c_int32), ("t_coarse_ms", ctypes.c_double)]
+                ("precond", ctypes.c_int32), ("n_coarse", ctypes.c_int32), ("t_coarse_ms", ctypes.c_double),
+                ("n_coarse_local", ctypes.c_int32), ("local_level", ctypes.c_int32), ("stagnated", ctypes.c_int32),
+                ("iteration_kind", ctypes.c_int32), ("abs_target", ctypes.c_double), ("floor_abs", ctypes.c_double),
+                ("rhs_norm", ctypes.c_double), ("spmv_kind", ctypes.c_int32), ("spmv_halo", ctypes.c_int32),
+                ("spmv_window_coverage", ctypes.c_double)]
 
 
 @dataclass
@@ -69,6 +73,16 @@ class SolveInfo:
     precond: str = "jacobi"
     n_coarse: int = 0
     t_coarse_ms: float = 0.0
+    n_coarse_local: int = 0
+    local_level: int = 0
+    stagnated: int = 0
+    iteration_kind: int = 1
+    abs_target: float = 0.0
+    floor_abs: float = 0.0
+    rhs_norm: float = 0.0
+    spmv_kind: int = 0
+    spmv_halo: int = 0
+    spmv_window_coverage: float = 0.0
 
 
 _lib = None
@@ -248,6 +262,9 @@ class Context:
         """``assemble_system`` (``padne/solver.py:783-812``); the CSR stays resident.  Returns nnz.
 
         All arrays host (numpy) or all device (torch cuda tensors)."""
+        # whatever was resident is about to be replaced: solver.solve_system must not mistake it for an earlier
+        # ResidentSystem (solver.assemble_flat sets the new token afterwards)
+        self._resident_token = None
         dev = _is_device(xy)
         if not dev:
             v_off, t_off = _np(v_off, np.int64), _np(t_off, np.int64)
@@ -277,6 +294,7 @@ class Context:
         return indptr, indices, data
 
     def set_csr(self, indptr, indices, data):
+        self._resident_token = None
         dev = _is_device(data)
         if not dev:
             indptr, indices, data = _np(indptr, np.int32), _np(indices, np.int32), _np(data, np.float64)
@@ -307,7 +325,10 @@ class Context:
         return v, SolveInfo(METHOD_NAMES.get(info.method, "?"), info.iterations, info.restarts,
                             info.n_constraints, info.rel_residual, info.residual_norm,
                             info.ground_node_current, info.t_setup_ms, info.t_krylov_ms, info.t_total_ms,
-                            PRECOND_NAMES.get(info.precond, "?"), info.n_coarse, info.t_coarse_ms)
+                            PRECOND_NAMES.get(info.precond, "?"), info.n_coarse, info.t_coarse_ms,
+                            info.n_coarse_local, info.local_level, info.stagnated, info.iteration_kind,
+                            info.abs_target, info.floor_abs, info.rhs_norm, info.spmv_kind, info.spmv_halo,
+                            info.spmv_window_coverage)
 
     def spmv(self, x):
         dev = _is_device(x)

@@ -31,9 +31,13 @@ struct Scal {
     int32_t max_iter, pad0, pad1, pad2;
     unsigned int ticket[4];
     double part[4];    // this rank's partial sums awaiting the all-reduce (multi-GPU)
+    // round-2 PCG iteration (pdn_cg2.cuh)
+    unsigned long long zmax_bits[2];   // bits of max|z_i| over this rank's rows, slot = iteration parity
+    double amax;                       // largest diagonal of the reduced operator (restriction scale, residual floor)
 };
 
-enum Mode { PLAIN = 0, CG = 1, BICG_V = 2, BICG_T = 3, RESID = 4 };
+// CG2: CG with the restriction of w and the coarse-residual recurrence in the tail (pdn_cg2.cuh)
+enum Mode { PLAIN = 0, CG = 1, BICG_V = 2, BICG_T = 3, RESID = 4, CG2 = 5 };
 
 // The reduced operator: main CSR part (rows flagged by a negative row pointer are skipped) plus a
 // tiny override CSR for the special rows (constraint terminals), handled by block 0.
@@ -109,10 +113,13 @@ __device__ __forceinline__ bool grid_reduce(double (&acc)[NACC], double *partial
 //   BICG_T: y = A x (x = sh);  ts = y.s, tt = y.y                         aux0 = s
 //   RESID : y = b - A x;       rr = y.y                                   aux0 = b
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
+__device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
 #include "pdn_peer_prim.cuh"
 #include "pdn_spmv.cuh"
 #include "pdn_sell.cuh"
 #include "pdn_coarse.cuh"
+#include "pdn_cg2.cuh"
 
 // scalar recurrences of the BiCGSTAB vector kernels (one thread, after the grid-wide reduction)
 __device__ __forceinline__ void bicg_x_finalize(const double (&acc)[3], Scal *sc) {
@@ -158,8 +165,6 @@ __global__ void scalar_kernel(Scal *sc, double *out) {
 // Two rows per thread (128-bit loads and stores, half the address arithmetic and half the warp collectives
 // of the restriction): the one-row version was instruction-issue bound (~250 instructions per 32 rows) once
 // the vectors stayed in L2.  r0 is a multiple of the sort window, so row pairs are the same on every rank count.
-__device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
-__device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
 
 template <bool TL>
 __global__ void __launch_bounds__(RPB) cg_update_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,

@@ -112,7 +112,8 @@ void pdn_peer_ensure(pdn_ctx *ctx, int64_t n) {
     const size_t words = PDN_PA_VEC + (size_t)PDN_PA_NVEC * n_cap;
     PDN_CUDA(cudaMalloc((void **)&c->arena, words * 8));
     PDN_CUDA(cudaMemsetAsync(c->arena, 0, words * 8, st));
-    PDN_CUDA(cudaMemsetAsync(c->epoch, 0, 4 * sizeof(unsigned long long), st));   // the wait-cycle counters [4..7] keep counting
+    PDN_CUDA(cudaMemsetAsync(c->epoch, 0, 4 * sizeof(unsigned long long), st));   // the wait-cycle counters [4..6] keep counting
+    PDN_CUDA(cudaMemsetAsync(c->epoch + 7, 0, sizeof(unsigned long long), st));   // epoch of the merged dots + c_w exchange
     PDN_CUDA(cudaMemsetAsync(c->ticket, 0, 4 * sizeof(unsigned int), st));
     // handles of all ranks (the all-gather also orders every rank's memset before any peer store)
     cudaIpcMemHandle_t mine;

@@ -8,6 +8,7 @@
 constexpr int PEER_MAX = PDN_PEER_MAX;
 constexpr size_t PA_HALO_FLAG = PDN_PA_HALO_FLAG, PA_RED_FLAG = PDN_PA_RED_FLAG, PA_RC_FLAG = PDN_PA_RC_FLAG;
 constexpr size_t PA_RED_VAL = PDN_PA_RED_VAL, PA_RC_VAL = PDN_PA_RC_VAL, PA_RC_SLOT = PDN_PA_RC_SLOT;
+constexpr size_t PA_CW_FLAG = PDN_PA_CW_FLAG, PA_CW_VAL = PDN_PA_CW_VAL;
 using PeerLink = PdnPeerLink;
 
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {

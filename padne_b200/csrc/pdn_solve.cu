@@ -173,6 +173,17 @@ struct SolveWork {
     DevBuf<float> co_Af2;
     int32_t nc2 = 0;
     DevBuf<unsigned int> co_counter;
+    std::string coarse_note;   // why the last build_coarse returned false ("" when it built)
+    int local_level = 0;       // 0: not requested, 1: built, < 0: requested but not built (-PDN_E* / -100: see build_coarse)
+    // round-2 PCG iteration (pdn_cg2.cuh): restriction tables of K1, coarse vectors kept by recurrence
+    bool v2 = false;           // this solve runs the three-kernel iteration
+    bool xs = true;            // SpMV with x-band staging (else the round-1 TMA-ring kernel)
+    XsPlan xsp{0, 1 << 28};
+    int xs_per_sm = 0;
+    double xs_coverage = 0.0;  // fraction of this rank's stored entries whose column falls inside the staged window
+    DevBuf<unsigned long long> tab, tab2, band_hist;
+    DevBuf<double> rc_d, cs_d, rc2_d, cs2_d;
+    double amax = 0.0;         // largest diagonal of the reduced operator
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
     DevBuf<double> partials;
@@ -280,6 +291,93 @@ static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, doub
 #endif
 }
 
+// ---- SELL SpMV with x-band staging (pdn_cg2.cuh) -------------------------------------------------------------
+static Cg2 make_cg2(SolveWork *w) {
+    Cg2 cg{};
+    cg.agg = w->agg.p;
+    cg.agg2 = w->nc2 > 0 ? w->agg2.p : nullptr;
+    cg.tab = w->tab.p;
+    cg.tab2 = w->tab2.p;
+    cg.rc = w->rc_d.p;
+    cg.cs = w->cs_d.p;
+    cg.rc2 = w->rc2_d.p;
+    cg.cs2 = w->cs2_d.p;
+    cg.nc = w->nc;
+    cg.nc2 = w->nc2;
+    return cg;
+}
+
+// CTAs of the x-staging kernel over `slices` slices: resident CTAs of the CG2 instantiation (every mode is launched
+// with the same grid, so that the staging plan fits them all)
+static int xs_grid(pdn_ctx *ctx, SolveWork *w, int64_t slices) {
+    if (!w->xs_per_sm) {
+        PDN_CUDA(cudaFuncSetAttribute(sell_xs_kernel<CG2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SX_SMEM));
+        int per_sm = 0;
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sell_xs_kernel<CG2, false>, SX_BLK, SX_SMEM));
+        w->xs_per_sm = per_sm < 1 ? 1 : per_sm;
+    }
+    int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * w->xs_per_sm, MAX_PART);
+    grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + SX_WARPS - 1) / SX_WARPS));
+    return (int)grid;
+}
+
+template <int MODE, bool DIST>
+static void launch_xs_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux, const Cg2 &cg) {
+    const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+    auto kern = sell_xs_kernel<MODE, DIST>;
+    static bool configured = false;
+    if (!configured) {
+        PDN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SX_SMEM));
+        configured = true;
+    }
+    PDN_LAUNCH_PDL(ctx, w->pdl, kern, xs_grid(ctx, w, slices), SX_BLK, SX_SMEM, w->A, w->xsp, x, y, aux, w->d_sc, w->partials.p,
+                   peer_link_or_none(ctx), cg);
+}
+
+// The staging plan of this rank's rows: band histogram of |col - row| on the device, then the smallest halo
+// (a multiple of 64 rows) whose window holds >= 99.5 % of the stored entries, the range of a CTA in ONE chunk
+// when rows + 2 halo fit the buffer, else in double-buffered chunks.  Out-of-window columns take the global path,
+// so any plan is correct; a mesh without locality (coverage low at every halo) just gathers through L2 as before.
+static void plan_xs(pdn_ctx *ctx, SolveWork *w) {
+    cudaStream_t st = ctx->stream;
+    const int64_t s0 = w->A.row_begin / SELL_C, s1 = (w->A.row_end + SELL_C - 1) / SELL_C, slices = s1 - s0;
+    w->xsp = XsPlan{0, 1 << 28};
+    w->xs_coverage = 0.0;
+    if (slices <= 0) return;
+    const int grid = xs_grid(ctx, w, slices);
+    const int64_t spc = (slices + grid - 1) / grid;          // slices of the longest CTA range
+    w->band_hist.reserve(64);
+    PDN_CUDA(cudaMemsetAsync(w->band_hist.p, 0, 64 * sizeof(unsigned long long), st));
+    PDN_LAUNCH(ctx, band_hist_kernel, pdn_grid(ctx, slices * 32, 256, 8), 256, 0, w->A, s0, s1, w->band_hist.p);
+    unsigned long long hist[64];
+    PDN_CUDA(cudaMemcpyAsync(hist, w->band_hist.p, sizeof hist, cudaMemcpyDeviceToHost, st));
+    PDN_CUDA(cudaStreamSynchronize(st));
+    double total = 0.0;
+    for (int b = 0; b < 64; b++) total += (double)hist[b];
+    if (!(total > 0.0)) return;
+    // largest halo the double-buffered layout can hold next to a useful chunk (>= 1024 rows)
+    const int halo_cap = std::min(63 * 64, ((SX_CAP / 2 - 1024) / 2) & ~63);
+    int halo = halo_cap;
+    double cum = 0.0, cov = 0.0;
+    for (int b = 0; b < 63; b++) {
+        cum += (double)hist[b];
+        const int h = 64 * (b + 1);
+        if (h > halo_cap) break;
+        cov = cum / total;
+        if (cov >= 0.995) { halo = h; break; }
+    }
+    if (const char *e = getenv("PADNE_B200_XS_HALO")) {       // tuning: force the halo (rows, rounded to 64)
+        halo = std::max(0, std::min(halo_cap, atoi(e) / 64 * 64));
+        cum = 0.0;
+        for (int b = 0; b < halo / 64; b++) cum += (double)hist[b];
+        cov = cum / total;
+    }
+    w->xs_coverage = cov;
+    w->xsp.halo = halo;
+    if (spc * SELL_C + 2 * halo <= SX_CAP) w->xsp.chunk_slices = (int32_t)std::max<int64_t>(spc, 1);
+    else w->xsp.chunk_slices = (SX_CAP / 2 - 2 * halo) / SELL_C;
+}
+
 template <int WHICH>
 static void dist_reduce(pdn_ctx *ctx, SolveWork *w);
 
@@ -287,12 +385,15 @@ static void dist_reduce(pdn_ctx *ctx, SolveWork *w);
 // the scalar recurrence runs in scalar_kernel; x must already hold the halo entries.
 template <int MODE>
 static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
+    const Cg2 no_cg{};
     if (is_dist(ctx)) {
-        launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
+        if (w->xs) launch_xs_kernel<MODE, true>(ctx, w, x, y, aux, no_cg);
+        else launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
         // peer memory: the kernel's last CTA has all-reduced the dots and run the recurrence itself
         if (MODE != PLAIN && !pdn_peer_enabled(ctx)) dist_reduce<MODE>(ctx, w);
     } else {
-        launch_sell_kernel<MODE, false>(ctx, w, x, y, aux);
+        if (w->xs) launch_xs_kernel<MODE, false>(ctx, w, x, y, aux, no_cg);
+        else launch_sell_kernel<MODE, false>(ctx, w, x, y, aux);
     }
 }
 
@@ -540,8 +641,11 @@ void build_elim(Elim &E, int64_t n, int64_t N, const std::vector<int32_t> &c_ptr
 namespace {
 
 struct KrylovResult {
-    int iterations = 0, restarts = 0;
+    int iterations = 0, restarts = 0, stagnated = 0;
     double rel_residual = 0.0;
+    double bnorm = 0.0;          // ||b||_2 of the reduced system
+    double abs_target = 0.0;     // the absolute bar the loop finally ran to
+    double floor_abs = 0.0;      // 4 u amax ||x||: what one fp64 residual evaluation can resolve
     float ms = 0.f;
 };
 
@@ -555,13 +659,15 @@ void reset_scal(pdn_ctx *ctx, SolveWork *w, double tol2, double bnorm2, int max_
     h.omega = 1.0;
     h.alpha = 1.0;
     h.gamma_old = 1.0;
+    h.amax = w->amax;
     *w->h_sc = h;
     PDN_CUDA(cudaMemcpyAsync(w->d_sc, w->h_sc, sizeof(Scal), cudaMemcpyHostToDevice, ctx->stream));
 }
 
-// keep the iteration counter / thresholds, restart the recurrences
-void restart_scal(pdn_ctx *ctx, SolveWork *w) {
+// keep the iteration counter, restart the recurrences (tol2: the threshold from now on)
+void restart_scal(pdn_ctx *ctx, SolveWork *w, double tol2) {
     Scal h = *w->h_sc;
+    h.tol2 = tol2;
     h.first = 1;
     h.done = 0;
     h.breakdown = 0;
@@ -647,6 +753,69 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     }
 }
 
+// ---- round-2 PCG iteration (pdn_cg2.cuh): K1 SpMV + restriction + recurrence, K2 coarse apply, K3 update + z ----
+static void launch_coarse_apply2(pdn_ctx *ctx, SolveWork *w) {
+    const int cgrid = (w->nc + CO_RB - 1) / CO_RB, cgrid2 = (w->nc2 + CO_RB - 1) / CO_RB;
+    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply2_kernel, cgrid + cgrid2, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_d.p, w->xc.p,
+                   cgrid, w->nc2, w->co_Af2.p, w->rc2_d.p, w->xc2.p);
+}
+
+template <bool ZONLY>
+static void launch_update2(pdn_ctx *ctx, SolveWork *w, int vgrid) {
+    const int64_t r0 = w->row_begin, r1 = w->row_end;
+    const int32_t *agg2 = w->nc2 > 0 ? w->agg2.p : nullptr;
+    const double *xc2 = w->nc2 > 0 ? w->xc2.p : nullptr;
+    if (halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0)) {
+        int which = -1;
+        for (int v = 0; v < PDN_PA_NVEC; v++)
+            if (w->z.p == pdn_peer_vec(ctx, v)) which = v;
+        if (which < 0) PDN_FAIL(PDN_ECUDA, "update: z is not inside the peer arena");
+        const int64_t npair = (r1 - r0 + 1) / 2;
+        const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));
+        PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<1024, ZONLY>), zgrid, 1024, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
+                       w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, pdn_peer_link_dev(ctx), w->halo.peer_d.p,
+                       pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx));
+    } else {
+        PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<RPB, ZONLY>), vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
+                       w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, (const PeerLink *)nullptr,
+                       (const HaloSend *)nullptr, (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr);
+    }
+}
+
+// exact restriction of the current r (start: also p = s = 0, c_s = 0, tables cleared); several GPUs: integer sum
+template <bool START>
+static void enqueue_pcg2_restrict(pdn_ctx *ctx, SolveWork *w, int vgrid) {
+    const int64_t r0 = w->row_begin, r1 = w->row_end;
+    const bool saved_pdl = w->pdl;
+    w->pdl = false;     // plain launches: these kernels do not call griddepcontrol.wait
+    PDN_LAUNCH(ctx, cg2_restrict_kernel<START>, vgrid, RPB, 0, r0, r1, w->d_sc, w->r.p, w->p.p, w->s.p, w->agg.p, w->rc_fix.p,
+               w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p);
+    if (is_dist(ctx))
+        PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, 0);
+    PDN_LAUNCH(ctx, cg2_convert_kernel<START>, std::max(1, (std::max(w->nc, w->nc2) + 255) / 256), 256, 0, w->d_sc, make_cg2(w),
+               w->rc_fix.p, w->rc_fix2.p);
+    w->pdl = saved_pdl;
+}
+
+void enqueue_pcg2_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
+    if (!halo_in_coarse_z(ctx, w)) halo_exchange(ctx, w, w->z.p);
+    const Cg2 cg = make_cg2(w);
+    if (is_dist(ctx)) launch_xs_kernel<CG2, true>(ctx, w, w->z.p, w->w.p, w->r.p, cg);
+    else launch_xs_kernel<CG2, false>(ctx, w, w->z.p, w->w.p, w->r.p, cg);
+    launch_coarse_apply2(ctx, w);
+    launch_update2<false>(ctx, w, vgrid);
+}
+
+// start / restart from the residual r
+void enqueue_pcg2_start(pdn_ctx *ctx, SolveWork *w, int vgrid) {
+    cudaStream_t st = ctx->stream;
+    PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
+    if (w->nc2 > 0) PDN_CUDA(cudaMemsetAsync(w->rc_fix2.p, 0, (size_t)2 * w->nc2 * sizeof(long long), st));
+    enqueue_pcg2_restrict<true>(ctx, w, vgrid);
+    launch_coarse_apply2(ctx, w);
+    launch_update2<true>(ctx, w, vgrid);
+}
+
 void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     const int64_t r0 = w->row_begin, r1 = w->row_end;
     const bool dist = is_dist(ctx);
@@ -686,12 +855,27 @@ void enqueue_bicg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
 // Multi-GPU: b, dinv and the operator are replicated; every rank iterates on its own rows and all
 // ranks see identical scalars (the all-reduce returns the same bits everywhere), so they take the
 // same decisions; x is all-gathered at the end.
-KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, double atol, int max_iter,
-                        int check_every) {
+//
+// Stopping (SolverInfo parity, padne/solver.py:775 and tests/test_solver.py:2083-2089): the reference's direct
+// solve leaves ||L v - r||_2 ~ 1e-10 and its own test bar is 1e-9 ABSOLUTE, while rtol = 1e-10 on a right-hand
+// side of norm ~2e3 stops at 2e-7.  So the loop stops when the TRUE residual of the reduced system is below
+//     min( rtol ||b||,  max( atol / 4,  4 u amax ||x||_2 ) )
+// -- the relative bar of the north star AND the reference's absolute one, the latter no lower than what fp64 can
+// resolve (u amax ||x|| is the rounding of one residual evaluation; below it the recurrence keeps shrinking but
+// b - A x does not: scripts/proto_v2_pcg.py).  The absolute target needs ||x||, so the loop first runs to
+// rtol ||b||, then tightens the threshold ONCE and simply continues (PCG: the recurrences are intact when `done`
+// latches; BiCGSTAB: restart from the true residual).  Stagnation above the target but below rtol ||b|| is
+// accepted and reported (stagnated = 1); above rtol ||b|| it is PDN_ENOTCONVERGED.
+struct KrylovTarget {
+    double rtol, atol_full;
+};
+
+KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, KrylovTarget tgt, int max_iter, int check_every) {
     KrylovResult res;
     const int64_t n = w->n;
     const int64_t r0 = w->row_begin, r1 = w->row_end;
     const bool dist = is_dist(ctx);
+    const bool v2 = w->v2 && method == PDN_METHOD_PCG;
     cudaStream_t st = ctx->stream;
     const int vgrid = pdn_grid(ctx, r1 - r0, RPB, 8);
     cudaEvent_t ev0, ev1;
@@ -707,6 +891,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     PDN_CUDA(cudaMemcpyAsync(&bnorm2, w->d_out, sizeof(double), cudaMemcpyDeviceToHost, st));
     PDN_CUDA(cudaStreamSynchronize(st));
     PDN_CUDA(cudaMemsetAsync(w->x.p, 0, n * sizeof(double), st));
+    res.bnorm = sqrt(bnorm2 > 0.0 ? bnorm2 : 0.0);
     if (!(bnorm2 > 0.0)) {  // b == 0 -> u == 0
         PDN_CUDA(cudaEventRecord(ev1, st));
         PDN_CUDA(cudaEventSynchronize(ev1));
@@ -715,8 +900,9 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         if (bnorm2 != bnorm2) PDN_FAIL(PDN_ESINGULAR, "solve: right-hand side is not finite");
         return res;
     }
-    double tol2 = rtol * rtol * bnorm2;
-    if (atol * atol > tol2) tol2 = atol * atol;
+    const double tol_req2 = tgt.rtol * tgt.rtol * bnorm2;      // the required bar: rtol ||b||
+    double tol2 = tol_req2;                                    // the bar in force (tightened once, below)
+    bool refined = !(tgt.atol_full > 0.0);
     reset_scal(ctx, w, tol2, bnorm2, max_iter);
     PDN_CUDA(cudaMemcpyAsync(w->r.p, w->b.p, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     if (dist) {
@@ -735,17 +921,21 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int per_iter = 0;
+    auto enqueue_iteration = [&]() {
+        if (v2) enqueue_pcg2_iteration(ctx, w, vgrid);
+        else if (method == PDN_METHOD_PCG) enqueue_pcg_iteration(ctx, w, vgrid);
+        else enqueue_bicg_iteration(ctx, w, vgrid);
+    };
     auto build_graph = [&]() {
         const int64_t launches_before = ctx->launches;
-        // PCG on one GPU: the four kernels of an iteration are chained by programmatic dependent launches
+        // PCG: the kernels of an iteration are chained by programmatic dependent launches (round-1 iteration:
+        // one GPU only; round-2 iteration: any number of GPUs, every kernel of the chain waits on its predecessor)
         const char *pdl_env = getenv("PADNE_B200_PDL");
-        w->pdl = method == PDN_METHOD_PCG && !dist && !(pdl_env && pdl_env[0] == '0');
+        w->pdl = method == PDN_METHOD_PCG && (v2 || !dist) && !(pdl_env && pdl_env[0] == '0');
         PDN_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         try {
-            for (int k = 0; k < check_every; k++) {
-                if (method == PDN_METHOD_PCG) enqueue_pcg_iteration(ctx, w, vgrid);
-                else enqueue_bicg_iteration(ctx, w, vgrid);
-            }
+            if (v2) enqueue_pcg2_restrict<false>(ctx, w, vgrid);      // r_c re-restricted once per graph launch
+            for (int k = 0; k < check_every; k++) enqueue_iteration();
         } catch (...) {
             w->pdl = false;
             cudaGraph_t g2 = nullptr;
@@ -767,13 +957,62 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
         cudaEventDestroy(ev0);
         cudaEventDestroy(ev1);
     };
+    // ||x||_2 of the current iterate (this rank's rows, summed over the ranks)
+    auto x_norm = [&]() -> double {
+        double xx = 0.0;
+        if (dist) {
+            PDN_LAUNCH(ctx, sumsq_kernel<true>, vgrid, RPB, 0, r0, r1, w->x.p, (const double *)nullptr, w->d_sc, w->d_out,
+                       w->partials.p);
+            dist_reduce<7>(ctx, w);
+        } else {
+            PDN_LAUNCH(ctx, sumsq_kernel<false>, vgrid, RPB, 0, r0, r1, w->x.p, (const double *)nullptr, w->d_sc, w->d_out,
+                       w->partials.p);
+        }
+        PDN_CUDA(cudaMemcpyAsync(&xx, w->d_out, sizeof(double), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        return sqrt(xx > 0.0 ? xx : 0.0);
+    };
+    // what one fp64 evaluation of b - A x can resolve: 4 u amax ||x||_2 (computed once, when first needed)
+    double floor_abs = -1.0;
+    auto get_floor = [&]() -> double {
+        if (floor_abs < 0.0) {
+            const Scal keep = *w->h_sc;                  // the reduction borrows the scalar block
+            floor_abs = 4.0 * 1.1102230246251565e-16 * w->amax * x_norm();
+            *w->h_sc = keep;
+            res.floor_abs = floor_abs;
+        }
+        return floor_abs;
+    };
+    // the absolute target once ||x|| is known; returns true when it tightened the bar in force
+    auto refine = [&]() -> bool {
+        if (refined) return false;
+        refined = true;
+        const double target = std::max(0.25 * tgt.atol_full, get_floor());
+        if (target * target < tol2 * 0.999) { tol2 = target * target; return true; }
+        return false;
+    };
+    // true residual good enough?  Exactly the bar in force, or -- once the bar is the absolute target, which
+    // sits next to the fp64 floor -- within 1.5x of it as long as the required rtol ||b|| holds
+    auto accepted = [&](double rr_true) { return rr_true <= std::max(tol2 * 1.0000001, std::min(tol2 * 2.25, tol_req2)); };
+    // stagnation: the required bar, but never below twice the floor (a request the arithmetic cannot meet)
+    auto acceptable_floor = [&](double rr_true) {
+        const double f = 2.0 * get_floor();
+        return rr_true <= std::max(tol_req2 * 1.0000001, f * f);
+    };
+    auto clear_tables = [&]() {
+        if (!v2) return;
+        PDN_CUDA(cudaMemsetAsync(w->tab.p, 0, (size_t)w->nc * TAB_STRIDE * sizeof(unsigned long long), st));
+        if (w->nc2 > 0) PDN_CUDA(cudaMemsetAsync(w->tab2.p, 0, (size_t)w->nc2 * TAB_STRIDE * sizeof(unsigned long long), st));
+    };
 
     try {
         const int max_restarts = 6;
         double best_rr = -1.0;
         for (int attempt = 0;; attempt++) {
             // start / restart from the current residual r
-            if (method == PDN_METHOD_PCG && w->two_level) {
+            if (v2) {
+                enqueue_pcg2_start(ctx, w, vgrid);
+            } else if (method == PDN_METHOD_PCG && w->two_level) {
                 PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
                 PDN_LAUNCH(ctx, cg_init_kernel<true>, vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->r.p, w->z.p, w->p.p,
                            w->s.p, w->agg.p, w->rc_fix.p, w->nc);
@@ -803,10 +1042,7 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 ctx->ktime = &kt;
                 kt.active = true;
                 kt.mark("start", st);
-                for (int k = 0; k < check_every; k++) {
-                    if (method == PDN_METHOD_PCG) enqueue_pcg_iteration(ctx, w, vgrid);
-                    else enqueue_bicg_iteration(ctx, w, vgrid);
-                }
+                for (int k = 0; k < check_every; k++) enqueue_iteration();
                 kt.active = false;
                 ctx->ktime = nullptr;
                 kt.report(pdn_comm_rank(ctx));
@@ -815,36 +1051,57 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, double rtol, dou
                 PDN_CUDA(cudaGraphLaunch(exec, st));
                 fetch_scal(ctx, w);
                 res.iterations = w->h_sc->iter;
-                ctx->launches += (int64_t)per_iter * check_every;  // kernels inside the graph
-                if (w->h_sc->done) break;
+                ctx->launches += (int64_t)per_iter * check_every + (v2 ? (dist ? 3 : 2) : 0);  // kernels inside the graph
+                if (!w->h_sc->done) continue;
+                // converged to the bar in force: the first time, bring in the absolute target (needs ||x||).
+                // PCG keeps going with the tighter bar -- `done` latched before anything was updated, so clearing
+                // it resumes the very same iteration; BiCGSTAB restarts from the true residual below.
+                if (w->h_sc->done == 1 && method == PDN_METHOD_PCG && w->h_sc->iter < max_iter && !refined) {
+                    const bool tighter = refine();
+                    Scal keep = *w->h_sc;
+                    memset(keep.ticket, 0, sizeof keep.ticket);
+                    if (tighter) { keep.done = 0; keep.tol2 = tol2; }
+                    *w->h_sc = keep;
+                    PDN_CUDA(cudaMemcpyAsync(w->d_sc, w->h_sc, sizeof(Scal), cudaMemcpyHostToDevice, st));
+                    if (tighter) {
+                        clear_tables();                 // K1's aborted launch left its restriction in them
+                        continue;
+                    }
+                }
+                break;
             }
+            const int done = w->h_sc->done;
             // true residual of the current x
             halo_exchange(ctx, w, w->x.p);
             launch_sell<RESID>(ctx, w, w->x.p, w->r.p, w->b.p);
             fetch_scal(ctx, w);
             const double rr_true = w->h_sc->rr;
             res.rel_residual = sqrt(rr_true / bnorm2);
-            const int done = w->h_sc->done;
             if (rr_true != rr_true) PDN_FAIL(PDN_ESINGULAR, "solve: residual is not finite (singular system?)");
-            if (rr_true <= tol2 * 1.0000001) break;
-            if (w->h_sc->iter >= max_iter)
+            if (done == 1 && method != PDN_METHOD_PCG) refine();   // BiCGSTAB: the restart below runs to the tightened bar
+            if (accepted(rr_true)) break;
+            if (w->h_sc->iter >= max_iter) {
+                if (rr_true <= tol_req2 * 1.0000001) { res.stagnated = 1; break; }    // the required bar holds
                 PDN_FAIL(PDN_ENOTCONVERGED, "solve: %d iterations, relative residual %.3e > %.3e", w->h_sc->iter,
-                         res.rel_residual, rtol);
-            // converged by the recurrence but not truly (drift), or breakdown: restart from the true residual
-            if (attempt >= max_restarts || (done == 1 && best_rr >= 0.0 && rr_true >= best_rr)) {
-                // stagnation at the attainable accuracy: accept if within 100x of the target, else fail
-                if (rr_true <= tol2 * 1e4) break;
-                PDN_FAIL(PDN_ENOTCONVERGED, "solve: stagnated at relative residual %.3e (target %.3e)",
-                         res.rel_residual, rtol);
+                         res.rel_residual, tgt.rtol);
+            }
+            // converged by the recurrence but not truly (drift, or the fp64 floor of b - A x), or breakdown:
+            // restart from the true residual, unless that stopped paying
+            if (attempt >= max_restarts || (done == 1 && best_rr >= 0.0 && rr_true >= 0.25 * best_rr)) {
+                if (acceptable_floor(rr_true)) { res.stagnated = 1; break; }    // the floor of the arithmetic
+                PDN_FAIL(PDN_ENOTCONVERGED, "solve: stagnated at relative residual %.3e (required %.3e)",
+                         res.rel_residual, tgt.rtol);
             }
             if (best_rr < 0.0 || rr_true < best_rr) best_rr = rr_true;
             res.restarts++;
-            restart_scal(ctx, w);
+            restart_scal(ctx, w, tol2);
+            clear_tables();
         }
     } catch (...) {
         cleanup();
         throw;
     }
+    res.abs_target = sqrt(tol2);
     if (dist) {   // every rank needs the whole u for the (replicated) recovery step
         try {
             pdn_comm_allgatherv(ctx, w->x.p, w->halo.begin.data());
@@ -1061,12 +1318,19 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     const int world = local ? std::max(1, w->halo.world) : 1;
     if (local) w->nc2 = 0;
     else { w->two_level = false; w->nc = 0; }
-    if (!ctx->geo_valid || ctx->geo_n_v <= 0 || ctx->geo_n_v > n) return false;
+    // every exit that leaves the level unbuilt says why (pdn_info / the bench line / the caller's error text)
+    auto fail = [&](const char *why) {
+        char buf[200];
+        snprintf(buf, sizeof buf, "%s coarse level not built: %s", local ? "rank-local" : "global", why);
+        w->coarse_note = buf;
+        return false;
+    };
+    if (!ctx->geo_valid || ctx->geo_n_v <= 0 || ctx->geo_n_v > n) return fail("no mesh geometry resident");
     // default: the inverse costs ~2.5 ms at 1600 aggregates and buys ~20% fewer iterations than 1024 at 1M rows
     if (target <= 0) target = n >= 200000 ? 1600 : 1024;
     if (target > CO_MAX) target = CO_MAX;
     if (target > (row_hi - row_lo) / 16) target = (int32_t)((row_hi - row_lo) / 16);     // tiny systems: keep >= 16 rows per aggregate
-    if (target < 4) return false;
+    if (target < 4) return fail("fewer than 64 rows");
     // bins are laid over ALL meshes; the local level keeps the ~1/world of them that hold its rows
     const int64_t raw_target = (int64_t)target * world;
 
@@ -1082,7 +1346,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         x0 = std::min(x0, hb[4 * b]); y0 = std::min(y0, hb[4 * b + 1]);
         x1 = std::max(x1, hb[4 * b + 2]); y1 = std::max(y1, hb[4 * b + 3]);
     }
-    if (!(x1 >= x0) || !(y1 >= y0)) return false;
+    if (!(x1 >= x0) || !(y1 >= y0)) return fail("degenerate bounding box");
 
     // bins: equal squares, about `target` aggregates in total
     CoarseGeom g{};
@@ -1103,7 +1367,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
             if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs <= std::max<int64_t>(raw_target, 4)) break;
             H *= 1.05;
         }
-        if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs > (int64_t)CO_MAX * world) return false;
+        if ((int64_t)g.n_mesh * g.nbx * g.nby + node_aggs > (int64_t)CO_MAX * world) return fail("more meshes + internal-node aggregates than CO_MAX");
         g.x0 = x0; g.y0 = y0; g.inv_h = 1.0 / H;
         g.n_bins = g.n_mesh * g.nbx * g.nby;
         const int32_t n_raw = g.n_bins + node_aggs;
@@ -1117,9 +1381,9 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         pdn_exclusive_scan_i32(ctx, w->co_used.p, n_raw, w->co_cid.p);
         PDN_CUDA(cudaMemcpyAsync(&nc, w->co_cid.p + n_raw, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         PDN_CUDA(cudaStreamSynchronize(st));
-        if (nc < 2) return false;
+        if (nc < 2) return fail("fewer than 2 non-empty aggregates");
         if (nc <= CO_MAX) break;
-        if (!local || attempt >= 6) return false;
+        if (!local || attempt >= 12) return fail("more non-empty bins than CO_MAX after 12 coarsenings");
         H *= 1.15;              // an uneven partition put more bins on this rank than the table holds: coarser bins
     }
     PDN_LAUNCH(ctx, agg_final_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->co_cid.p, agg.p);
@@ -1132,7 +1396,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     PDN_CUDA(cudaStreamSynchronize(st));
     double dmin = 1e300;
     for (double v : hm) dmin = std::min(dmin, v);
-    if (!(dmin > 0.0) || !(dmin < 1e300)) return false;
+    if (!(dmin > 0.0) || !(dmin < 1e300)) return fail("non-positive Jacobi diagonal");
     const double amax = 1.0 / dmin;
     const double fix = exp2(floor(log2(4.0e18 / ((double)std::max<int64_t>(n_entries, 1) * amax))));
 
@@ -1154,7 +1418,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     int32_t R = (int32_t)std::min<int64_t>(16, (int64_t)(200 * 1024) / ((int64_t)nc * 8));
     if (const char *e = getenv("PADNE_B200_CO_R")) R = std::min<int32_t>(R, std::max(1, atoi(e)));   // tuning
     R = std::max(R, (nc + ctx->n_sm - 1) / ctx->n_sm);
-    if (R < 1 || R > 16) return false;
+    if (R < 1 || R > 16) return fail("inverse: rows per CTA out of range");
     const int grid = (nc + R - 1) / R;
     const size_t smem = (size_t)R * nc * sizeof(double);
     static size_t smem_set = 0;
@@ -1162,7 +1426,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         PDN_CUDA(cudaFuncSetAttribute(coarse_invert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(220 * 1024)));
         smem_set = 220 * 1024;
     }
-    if (smem > 220 * 1024) return false;
+    if (smem > 220 * 1024) return fail("inverse: rows do not fit shared memory");
     w->co_piv.reserve((size_t)grid * ((size_t)R * nc + 256));
     w->co_counter.reserve((size_t)grid + 4);
     PDN_CUDA(cudaMemsetAsync(w->co_counter.p, 0, ((size_t)grid + 4) * sizeof(unsigned int), st));
@@ -1183,7 +1447,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     if (stt != 0) {   // not positive definite (or a stuck barrier): fall back to Jacobi, loudly in last_error
         pdn_status_reset(ctx);
         ctx->last_error = std::string("coarse matrix inversion failed (") + pdn_strerror(stt) + "): Jacobi only";
-        return false;
+        return fail(stt == PDN_ESINGULAR ? "inverse: non-positive pivot" : "inverse: a CTA missed its deadline");
     }
     rc_fix.reserve((size_t)2 * nc);
     xc.reserve((size_t)nc);
@@ -1261,10 +1525,13 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     if (opts_in) opts = *opts_in;
     else opts.n_nodes = -1;
     const double rtol = opts.rtol > 0.0 ? opts.rtol : 1e-10;
-    const double atol = opts.atol > 0.0 ? opts.atol : 0.0;
+    // absolute bar on ||L v - r||_2 (the reference's own: tests/test_solver.py:2083-2089); < 0 switches it off
+    const double atol = opts.atol > 0.0 ? opts.atol : (opts.atol < 0.0 ? 0.0 : 1e-9);
     const int max_iter = opts.max_iter > 0 ? opts.max_iter : (int)(20.0 * sqrt((double)N)) + 2000;
     const int check_every = opts.check_every > 0 ? opts.check_every : 32;
-    if (opts.precond == PDN_PRECOND_AMG) PDN_FAIL(PDN_EUNSUPPORTED, "solve: AMG preconditioner not built in this version");
+    if (opts.precond != PDN_PRECOND_AUTO && opts.precond != PDN_PRECOND_NONE && opts.precond != PDN_PRECOND_TWOLEVEL &&
+        opts.precond != PDN_PRECOND_JACOBI)
+        PDN_FAIL(PDN_EINVAL, "solve: unknown preconditioner %d", opts.precond);
 
     cudaEvent_t ev_start, ev_setup, ev_end;
     PDN_CUDA(cudaEventCreate(&ev_start));
@@ -1488,6 +1755,15 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         PDN_LAUNCH(ctx, scatter_f64_kernel, pdn_blocks(nT, BLK), BLK, 0, nT, w->sp_row.p, w->tmp_f64b.p, w->dinv.p);
     }
     PDN_LAUNCH(ctx, check_dinv_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, w->dinv.p, ctx->d_status);
+    // largest diagonal of the reduced operator: scale of the K1 restriction and of the residual floor
+    std::vector<double> h_dmin;
+    {
+        const int mgrid = pdn_grid(ctx, n, CO_BLK, 4);
+        w->co_tmp.reserve((size_t)mgrid + 8);
+        PDN_LAUNCH(ctx, min_kernel, mgrid, CO_BLK, 0, n, w->dinv.p, w->co_tmp.p);
+        h_dmin.resize((size_t)mgrid);
+        PDN_CUDA(cudaMemcpyAsync(h_dmin.data(), w->co_tmp.p, h_dmin.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
     if (opts.precond == PDN_PRECOND_NONE) PDN_LAUNCH(ctx, ones_kernel, pdn_grid(ctx, n, BLK, 8), BLK, 0, n, w->dinv.p);
     {
         int64_t detail = 0;
@@ -1499,6 +1775,9 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
                 PDN_CUDA(cudaMemcpy(&node, w->perm.p + detail, sizeof(int32_t), cudaMemcpyDeviceToHost));
             PDN_FAIL(stt, "solve: node %d has no conductance to any other node (%s)", node, pdn_strerror(stt));
         }
+        double dmin = 1e300;
+        for (double v : h_dmin) dmin = std::min(dmin, v);
+        w->amax = dmin > 0.0 && dmin < 1e300 ? 1.0 / dmin : 0.0;
     }
     w->n_special = nT;
     w->A.n = n;
@@ -1530,6 +1809,14 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     }
     w->have_operator = true;
     trace.mark("halo_plan");
+    // SpMV kernel of the Krylov loop: x-band staging (pdn_cg2.cuh) unless PADNE_B200_SPMV=ring asks for the
+    // round-1 TMA-ring kernel (A/B measurements)
+    {
+        const char *e = getenv("PADNE_B200_SPMV");
+        w->xs = !(e && strcmp(e, "ring") == 0);
+        if (w->xs) plan_xs(ctx, w);
+        trace.mark("xs_plan");
+    }
 
     // second level of the preconditioner (systems assembled from meshes: the aggregates are coordinate bins)
     w->two_level = false;
@@ -1561,22 +1848,59 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             if (!ok && opts.precond == PDN_PRECOND_TWOLEVEL)
                 PDN_FAIL(PDN_EUNSUPPORTED, "solve: no coarse space could be built (%s)", ctx->last_error.c_str());
             // several GPUs, PCG: a second, rank-local level keeps the bins as fine as on one GPU (the global level
-            // is capped at CO_MAX aggregates for the whole board); every rank must take the same decision,
-            // so a rank whose local level cannot be built runs with nc2 = 0 but still launches the same kernels
+            // is capped at CO_MAX aggregates for the whole board).  PADNE_B200_LOCAL_LEVEL: 0 off, 1 on, "try" on but
+            // optional; default: on from 4 ranks.  Every rank must take the same decision, so the outcome is summed
+            // over the ranks: unless optional, ONE rank that cannot build its level fails the solve on ALL ranks,
+            // with the reason -- round 1 fell back silently and lost 1.8x in iterations at 8 GPUs.
             w->nc2 = 0;
-            // Measured: on 2 GPUs it saves 16 % of the iterations but costs 20 % per iteration (second restriction
-            // and apply), so it is the default from 4 ranks on; PADNE_B200_LOCAL_LEVEL=0/1 overrides (same on all ranks).
+            w->local_level = 0;
             const char *le = getenv("PADNE_B200_LOCAL_LEVEL");
+            const bool optional = le && strcmp(le, "try") == 0;
             const bool want_local = le ? le[0] != '0' : pdn_comm_world(ctx) >= 4;
             if (ok && is_dist(ctx) && method == PDN_METHOD_PCG && want_local) {
-                try {
-                    build_coarse(ctx, w, opts.n_coarse, (int64_t)sell_total + (int64_t)r_ci.size(), E.symmetric, /*local=*/true);
-                } catch (...) {
-                    cudaEventDestroy(c0);
-                    cudaEventDestroy(c1);
-                    throw;
+                const auto t_loc0 = std::chrono::steady_clock::now();
+                const bool built = build_coarse(ctx, w, opts.n_coarse, (int64_t)sell_total + (int64_t)r_ci.size(), E.symmetric,
+                                                /*local=*/true);
+                const std::string note = built ? std::string() : w->coarse_note;
+                w->tmp_f64a.reserve(4);
+                const double mine = built ? 0.0 : 1.0;
+                PDN_CUDA(cudaMemcpyAsync(w->tmp_f64a.p, &mine, sizeof(double), cudaMemcpyHostToDevice, st));
+                pdn_comm_allreduce_sum(ctx, w->tmp_f64a.p, 1);
+                double failed = 0.0;
+                PDN_CUDA(cudaMemcpyAsync(&failed, w->tmp_f64a.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+                PDN_CUDA(cudaStreamSynchronize(st));
+                if (failed > 0.0) {
+                    fprintf(stderr, "[padne_b200 rank %d] rank-local coarse level: %d of %d ranks could not build it%s%s\n",
+                            pdn_comm_rank(ctx), (int)failed, pdn_comm_world(ctx), built ? "" : " -- this rank: ", note.c_str());
+                    if (!optional) {
+                        PDN_FAIL(PDN_EUNSUPPORTED, "solve: the rank-local coarse level failed on %d of %d ranks (%s); "
+                                 "PADNE_B200_LOCAL_LEVEL=try makes it optional, =0 switches it off", (int)failed,
+                                 pdn_comm_world(ctx), built ? "built here" : note.c_str());
+                    }
+                    w->nc2 = 0;               // optional: every rank drops it
+                    w->local_level = -1;
+                } else {
+                    w->local_level = 1;
                 }
+                // build_coarse ends with a stream synchronisation, so wall clock is the device time here
+                w->coarse_ms += (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_loc0).count();
             }
+        }
+    }
+    // round-2 iteration (three kernels, one exchange): PCG + two-level + the x-staging SpMV; with several GPUs it
+    // needs the peer-memory link (the NCCL fallback keeps the round-1 iteration).  PADNE_B200_PCG=v1 forces round 1.
+    {
+        const char *e = getenv("PADNE_B200_PCG");
+        w->v2 = method == PDN_METHOD_PCG && w->two_level && w->xs && (!is_dist(ctx) || pdn_peer_enabled(ctx)) &&
+                !(e && strcmp(e, "v1") == 0);
+        if (w->v2) {
+            w->tab.reserve((size_t)w->nc * TAB_STRIDE + 8);
+            w->tab2.reserve((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8);
+            w->rc_d.reserve((size_t)w->nc + 8); w->cs_d.reserve((size_t)w->nc + 8);
+            w->rc2_d.reserve((size_t)std::max(w->nc2, 1) + 8); w->cs2_d.reserve((size_t)std::max(w->nc2, 1) + 8);
+            if (w->nc2 == 0) { w->rc_fix2.reserve(8); w->xc2.reserve(8); w->co_Af2.reserve(8); }
+            PDN_CUDA(cudaMemsetAsync(w->tab.p, 0, ((size_t)w->nc * TAB_STRIDE + 8) * sizeof(unsigned long long), st));
+            PDN_CUDA(cudaMemsetAsync(w->tab2.p, 0, ((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8) * sizeof(unsigned long long), st));
         }
     }
 
@@ -1603,7 +1927,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     trace.mark("vectors");
 
     // ---- Krylov -------------------------------------------------------------------------------------
-    KrylovResult kr = run_krylov(ctx, w, method, rtol, atol, max_iter, check_every);
+    KrylovResult kr = run_krylov(ctx, w, method, KrylovTarget{rtol, atol}, max_iter, check_every);
 
     trace.mark("krylov");
     if (is_dist(ctx)) {   // a peer that never answered (pdn_peer.cuh deadline)
@@ -1666,6 +1990,16 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
                                      : (opts.precond == PDN_PRECOND_NONE ? PDN_PRECOND_NONE : PDN_PRECOND_JACOBI);
         info->n_coarse = w->two_level ? w->nc : 0;
         info->t_coarse_ms = w->coarse_ms;
+        info->n_coarse_local = w->nc2;
+        info->local_level = w->local_level;
+        info->stagnated = kr.stagnated;
+        info->iteration_kind = w->v2 && method == PDN_METHOD_PCG ? 2 : 1;
+        info->abs_target = kr.abs_target;
+        info->floor_abs = kr.floor_abs;
+        info->rhs_norm = kr.bnorm;
+        info->spmv_kind = w->xs ? 1 : 0;
+        info->spmv_halo = w->xs ? w->xsp.halo : 0;
+        info->spmv_window_coverage = w->xs ? w->xs_coverage : 0.0;
     }
 }
 
@@ -1714,8 +2048,28 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
     // synchronises once at the end, like the kernels inside the solver's CUDA graph.
     reset_scal(ctx, w, 0.0, 0.0, -1);
     const int64_t r0 = sell ? w->row_begin : 0, r1 = sell ? w->row_end : n;
+    // the kernel exactly as the last solve ran it: CG2 (restriction + recurrence tail) for the round-2 iteration.
+    // Peer exchanges are left out (null link): this rank's launch only.
+    const bool v2 = sell && w->v2;
+    const Cg2 cg = v2 ? make_cg2(w) : Cg2{};
+    if (v2) {
+        w->h_sc->amax = w->amax;
+        w->h_sc->zmax_bits[0] = w->h_sc->zmax_bits[1] = (unsigned long long)0x3ff0000000000000ull;   // max|z| = 1.0
+        PDN_CUDA(cudaMemcpyAsync(w->d_sc, w->h_sc, sizeof(Scal), cudaMemcpyHostToDevice, st));
+    }
     auto launch = [&]() {
-        if (sell) {
+        if (sell && w->xs) {
+            const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+            if (v2) {
+                PDN_CUDA(cudaFuncSetAttribute(sell_xs_kernel<CG2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SX_SMEM));
+                PDN_LAUNCH(ctx, (sell_xs_kernel<CG2, false>), xs_grid(ctx, w, slices), SX_BLK, SX_SMEM, w->A, w->xsp, x.p, y.p, aux.p,
+                           w->d_sc, w->partials.p, (const PeerLink *)nullptr, cg);
+            } else {
+                PDN_CUDA(cudaFuncSetAttribute(sell_xs_kernel<CG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SX_SMEM));
+                PDN_LAUNCH(ctx, (sell_xs_kernel<CG, false>), xs_grid(ctx, w, slices), SX_BLK, SX_SMEM, w->A, w->xsp, x.p, y.p, aux.p,
+                           w->d_sc, w->partials.p, (const PeerLink *)nullptr, cg);
+            }
+        } else if (sell) {
             launch_sell_kernel<CG, false>(ctx, w, x.p, y.p, aux.p);
         } else {
             launch_spmv<CG>(ctx, Afull, x.p, y.p, aux.p, w);
@@ -1729,7 +2083,13 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
         PDN_CUDA(cudaEventRecord(ev[2 * k], st));
         launch();
         PDN_CUDA(cudaEventRecord(ev[2 * k + 1], st));
-        if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
+        if (mode == 2 && v2) {   // the rest of a round-2 iteration: K2, K3 (dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux)
+            launch_coarse_apply2(ctx, w);
+            PDN_LAUNCH(ctx, (cg_update2_kernel<RPB, false>), pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p,
+                       v3.p, v4.p, v5.p, aux.p, w->agg.p, w->xc.p, w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr,
+                       w->nc2 > 0 ? w->xc2.p : (const double *)nullptr, (const PeerLink *)nullptr, (const HaloSend *)nullptr,
+                       (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr);
+        } else if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
             PDN_LAUNCH(ctx, cg_update_kernel<false>, pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p,
                        v3.p, v4.p, v5.p, aux.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
     }

@@ -29,7 +29,21 @@ def test_strerror_and_struct_layout():
     assert b"singular" in lib.pdn_strerror(capi.PDN_ESINGULAR)
     assert lib.pdn_strerror(capi.PDN_ENONMANIFOLD) == b"Non-manifold mesh"
     assert ctypes.sizeof(capi.PdnOpts) == 48
-    assert ctypes.sizeof(capi.PdnInfo) == 88
+    assert ctypes.sizeof(capi.PdnInfo) == 144
+    # the ctypes mirrors against the header itself: gcc prints the C sizes and the offset of the last field
+    import subprocess
+    import tempfile
+    src = ('#include <stdio.h>\n#include <stddef.h>\n#include "padne_b200.h"\n'
+           'int main(void){printf("%zu %zu %zu", sizeof(pdn_opts), sizeof(pdn_info), '
+           'offsetof(pdn_info, spmv_window_coverage));return 0;}\n')
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "s.c")
+        open(c, "w").write(src)
+        exe = os.path.join(d, "s")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
+        so, si, off = map(int, subprocess.check_output([exe]).split())
+    assert (so, si) == (ctypes.sizeof(capi.PdnOpts), ctypes.sizeof(capi.PdnInfo))
+    assert off == capi.PdnInfo.spmv_window_coverage.offset
 
 
 def test_no_gpu_means_loud_failure():
