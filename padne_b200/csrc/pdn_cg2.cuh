@@ -15,13 +15,13 @@
 // restricted r in the update kernel (match.any / redux on its critical path: 12-15 us against 5 us for the
 // plain update).  Here the restriction rides in the SpMV, whose issue slots are idle while it waits for HBM.
 //
-// Restriction arithmetic: 32-bit FIXED POINT per entry, 64-bit integer atomics per (warp, aggregate) into a
-// table whose entries sit TAB_STRIDE words apart (atomics on one cache line serialise in L2).  Integer sums are
-// order-independent, so the solve stays bit-reproducible run to run.  Scale: |w_i| <= 2 a_ii max|z| for a
-// diagonally dominant row, so fix = 2^25 / (8 amax zmax) can never overflow a lane's int32 (clamped anyway);
-// zmax is the maximum the previous K3 (or the start kernel) left in sc->zmax_bits.  r_c is re-restricted from r
-// once per CUDA-graph launch (every check_every iterations), so quantisation drift cannot accumulate
-// (scripts/proto_v2_pcg.py: same iteration count as textbook PCG, drift of r_c <= 5e-2 of its norm).
+// Restriction arithmetic: 42-bit FIXED POINT per entry (2^38 steps per scale), 64-bit integer atomics per
+// (warp, aggregate) into a table whose entries sit TAB_STRIDE words apart (atomics on one cache line serialise in
+// L2).  Integer sums are order-independent, so the solve stays bit-reproducible run to run.  Scale: |w_i| <=
+// 2 a_ii max|z| for a diagonally dominant row, so fix = 2^38 / (8 amax zmax) cannot clip; zmax is the maximum
+// the previous K3 (or the start kernel) left in sc->zmax_bits.  r_c is re-restricted from r once per CUDA-graph
+// launch (every check_every iterations) at the same resolution, so drift cannot accumulate
+// (scripts/proto_v2_pcg.py: same iteration count as textbook PCG, drift of r_c <= 1e-3 of its norm).
 //
 // x-band staging (north star kernel 3): a CTA owns a contiguous range of SELL slices; in mesh-local numbering
 // the columns of its rows sit within +-halo of the rows themselves (one grid row + the sort window), so the
@@ -34,25 +34,11 @@
 // Included by pdn_kernels.cuh (namespace pdnk) after pdn_sell.cuh and pdn_coarse.cuh.
 #pragma once
 
-constexpr int TAB_STRIDE = 8;          // words between two accumulators of the restriction table (64 B)
 constexpr int SX_WARPS = 16;
 constexpr int SX_BLK = SX_WARPS * 32;
 constexpr int SX_CAP = 13824;          // doubles of shared memory for x windows per CTA (108 KB -> 2 CTAs per SM)
 constexpr int SX_U = 8;                // entries per row fetched per step
 constexpr size_t SX_SMEM = (size_t)SX_CAP * 8;
-constexpr int Q_LIM = 33554431;        // 2^25 - 1: 32 lanes cannot overflow int32
-constexpr double Q_STEPS = 33554432.0; // 2^25
-constexpr double W_BOUND = 8.0;        // headroom over the diagonal-dominance bound 2 a_ii max|z|
-
-// what K1 needs beyond the operator: aggregates, restriction tables, the coarse vectors kept by recurrence
-struct Cg2 {
-    const int32_t *agg;               // [n] global-level aggregate of every row (-1: none)
-    const int32_t *agg2;              // rank-local level (null without one)
-    unsigned long long *tab, *tab2;   // [nc * TAB_STRIDE] fixed-point accumulators of c_w (zero between launches)
-    double *rc, *cs;                  // [nc] coarse residual P^T r and P^T s
-    double *rc2, *cs2;                // the same for the rank-local level
-    int32_t nc, nc2;
-};
 
 // how the CTAs stage x (host: plan_xs in pdn_solve.cu)
 struct XsPlan {
@@ -69,124 +55,6 @@ __device__ __forceinline__ int32_t ld_hint(const int32_t *p, uint64_t pol) {
     int32_t v;
     asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
     return v;
-}
-__device__ __forceinline__ void red_add_u64(unsigned long long *p, unsigned long long v) {
-    asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-// c_w[a] += val over the lanes of a warp (all 32 lanes call; a < 0 contributes nothing)
-template <int STRIDE = TAB_STRIDE>
-__device__ __forceinline__ void restrict32(double val, int32_t a, double fix, unsigned long long *tab) {
-    int q = __double2int_rn(val * fix);
-    q = max(min(q, Q_LIM), -Q_LIM);
-    const unsigned peers = __match_any_sync(0xffffffffu, a);
-    const int sum = __reduce_add_sync(peers, q);
-    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && a >= 0 && sum != 0)
-        red_add_u64(tab + (size_t)a * STRIDE, (unsigned long long)(long long)sum);
-}
-
-__device__ __forceinline__ double restrict_fix(const Scal *sc) {
-    const double zmax = __longlong_as_double((long long)sc->zmax_bits[sc->iter & 1]);
-    const double bound = W_BOUND * sc->amax * zmax;
-    return bound > 0.0 && bound < 1e300 ? Q_STEPS / bound : 0.0;
-}
-
-// ---- the tail of K1: all threads of the LAST CTA call; thread 0 holds the grid totals of the three dots -------
-template <bool DIST>
-__device__ __forceinline__ void cg2_tail(double (&acc)[3], Scal *sc, const Cg2 &cg, const PeerLink *Lp, double fix) {
-    __shared__ double sh[4];
-    __shared__ int sh_done, sh_ok;
-    const int tid = threadIdx.x, nt = blockDim.x;
-    const double invfix = fix > 0.0 ? 1.0 / fix : 0.0;
-    const volatile long long *src = nullptr;       // several GPUs: the slots of all ranks in the local arena
-    if (DIST && Lp != nullptr) {
-        // ONE exchange: every rank stores [gamma, delta, rr, 1/fix, q[0..nc)] into its slot on every rank
-        const PeerLink &L = *Lp;
-        const unsigned long long e = L.epoch[7] + 1;
-        const size_t slot = (size_t)(e & 1) * PEER_MAX;
-        if (tid == 0) { peer_log(L, 0); sh[0] = acc[0]; sh[1] = acc[1]; sh[2] = acc[2]; sh[3] = invfix; sh_ok = 1; }
-        __syncthreads();
-        for (int k = 0; k < L.world; k++) {
-            long long *dst = reinterpret_cast<long long *>(L.arena[k] + PA_CW_VAL) + (slot + L.me) * PA_RC_SLOT;
-            if (tid < 4) reinterpret_cast<double *>(dst)[tid] = sh[tid];
-            for (int j = tid; j < cg.nc; j += nt) dst[4 + j] = (long long)__ldcg(cg.tab + (size_t)j * TAB_STRIDE);
-        }
-        __threadfence_system();
-        __syncthreads();
-        if (tid < L.world) st_release_sys(L.arena[tid] + PA_CW_FLAG + slot + L.me, e);
-        if (tid < L.world && !peer_wait(L.arena[L.me] + PA_CW_FLAG + slot + tid, e, L.status, L.epoch + 5)) sh_ok = 0;
-        __syncthreads();
-        src = reinterpret_cast<const volatile long long *>(L.arena[L.me] + PA_CW_VAL) + slot * PA_RC_SLOT;
-        if (tid == 0) {
-            L.epoch[7] = e;
-            peer_log(L, 1);
-            acc[0] = acc[1] = acc[2] = 0.0;
-            for (int r = 0; r < L.world; r++) {       // rank order: identical bits on every rank
-                const volatile double *h = reinterpret_cast<const volatile double *>(src + (size_t)r * PA_RC_SLOT);
-                acc[0] += h[0]; acc[1] += h[1]; acc[2] += h[2];
-            }
-        }
-    }
-    if (tid == 0) {
-        if (DIST && Lp != nullptr && !sh_ok) { sc->done = 3; sc->breakdown = 1; }
-        else spmv_finalize<CG>(acc, sc);
-        sh[0] = sc->alpha;
-        sh[1] = sc->beta;
-        sh_done = sc->done;
-        sc->zmax_bits[sc->iter & 1] = 0ull;     // the slot the coming K3 maximises into (iter already advanced)
-    }
-    __syncthreads();
-    if (sh_done) return;                        // identical on every rank; the host clears the tables before a restart
-    const double alpha = sh[0], beta = sh[1];
-    for (int j = tid; j < cg.nc; j += nt) {
-        double cw;
-        if (DIST && Lp != nullptr) {
-            cw = 0.0;
-            for (int r = 0; r < Lp->world; r++) {
-                const volatile long long *s = src + (size_t)r * PA_RC_SLOT;
-                cw += (double)s[4 + j] * reinterpret_cast<const volatile double *>(s)[3];
-            }
-        } else {
-            cw = (double)(long long)__ldcg(cg.tab + (size_t)j * TAB_STRIDE) * invfix;
-        }
-        cg.tab[(size_t)j * TAB_STRIDE] = 0ull;
-        const double c = cw + beta * cg.cs[j];
-        cg.cs[j] = c;
-        cg.rc[j] -= alpha * c;
-    }
-    for (int j = tid; j < cg.nc2; j += nt) {    // rank-local level: block diagonal, nothing to exchange
-        const double cw = (double)(long long)__ldcg(cg.tab2 + (size_t)j * TAB_STRIDE) * invfix;
-        cg.tab2[(size_t)j * TAB_STRIDE] = 0ull;
-        const double c = cw + beta * cg.cs2[j];
-        cg.cs2[j] = c;
-        cg.rc2[j] -= alpha * c;
-    }
-}
-
-// override rows (constraint terminals) for CG2: as special_rows, plus the restriction of their w entries
-__device__ __forceinline__ void special_rows_cg2(const SellOp &A, const double *__restrict__ x, double *__restrict__ y,
-                                                 const double *__restrict__ aux0, double (&acc)[3], int32_t gwarp,
-                                                 int32_t n_gwarp, const Cg2 &cg, double fix) {
-    const int lane = threadIdx.x & 31;
-    for (int32_t t = gwarp; t < A.n_special; t += n_gwarp) {
-        const int32_t row = A.sp_row[t];
-        if (row < A.row_begin || row >= A.row_end) continue;
-        double s2 = 0.0;
-        for (int32_t q = A.sp_rp[t] + lane; q < A.sp_rp[t + 1]; q += 32) s2 = fma(A.sp_va[q], x[A.sp_ci[q]], s2);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-        if (lane == 0) {
-            row_epilogue<CG>(row, s2, x[row], aux0[row], y, acc);
-            int q = __double2int_rn(s2 * fix);
-            q = max(min(q, Q_LIM), -Q_LIM);
-            const int32_t a = cg.agg[row];
-            if (a >= 0 && q != 0) red_add_u64(cg.tab + (size_t)a * TAB_STRIDE, (unsigned long long)(long long)q);
-            if (cg.nc2 > 0) {
-                const int32_t a2 = cg.agg2[row];
-                if (a2 >= 0 && q != 0) red_add_u64(cg.tab2 + (size_t)a2 * TAB_STRIDE, (unsigned long long)(long long)q);
-            }
-        }
-    }
 }
 
 // ---- K1 ---------------------------------------------------------------------------------------------------
@@ -311,8 +179,8 @@ __global__ void __launch_bounds__(SX_BLK, 2) sell_xs_kernel(SellOp A, XsPlan P, 
             }
             if (live) row_epilogue<EMODE>(row, sum, xi, ai, y, acc);
             if (MODE == CG2) {
-                restrict32(sum, a1, fix, cg.tab);
-                if (cg.nc2 > 0) restrict32(sum, a2, fix, cg.tab2);
+                restrict_q(sum, a1, fix, cg.tab);
+                if (cg.nc2 > 0) restrict_q(sum, a2, fix, cg.tab2);
             }
             s = sn; off = n_off; off1 = n_off1; mask = n_mask; w = wn;
         }
@@ -532,7 +400,8 @@ __global__ void __launch_bounds__(BLK) cg_update2_kernel(int64_t r0, int64_t n, 
 }
 
 // ---- start / resync -------------------------------------------------------------------------------------------
-// exact restriction of r into the 32-bit fixed-point accumulator rc_fix (slot 0), scaled by ||r|| as in round 1;
+// restriction of r into the fixed-point accumulator rc_fix (slot 0), 2^38 steps per ||r||_2 (as precise as K1's:
+// an error made here stays in r_c until the next re-restriction);
 // START also clears p and s.  Followed (several GPUs) by the integer sum over the ranks and by cg2_convert_kernel.
 template <bool START>
 __global__ void __launch_bounds__(RPB) cg2_restrict_kernel(int64_t r0, int64_t n, const Scal *__restrict__ sc,
@@ -541,7 +410,7 @@ __global__ void __launch_bounds__(RPB) cg2_restrict_kernel(int64_t r0, int64_t n
                                                            long long *rc_fix, const int32_t *__restrict__ agg2,
                                                            long long *rc_fix2) {
     if (!START && sc->done) return;
-    const double fix = CO_RFIX32 / sqrt(fmax(sc->rr, 1e-300));
+    const double fix = Q_STEPS / sqrt(fmax(sc->rr, 1e-300));
     unsigned long long *rc = reinterpret_cast<unsigned long long *>(rc_fix);
     unsigned long long *rc2 = reinterpret_cast<unsigned long long *>(rc_fix2);
     for (int64_t i0 = r0 + (int64_t)blockIdx.x * RPB; i0 < n; i0 += (int64_t)gridDim.x * RPB) {
@@ -552,8 +421,8 @@ __global__ void __launch_bounds__(RPB) cg2_restrict_kernel(int64_t r0, int64_t n
             ri = r[i];
             if (START) { p[i] = 0.0; s[i] = 0.0; }
         }
-        restrict32<1>(ri, act ? agg[i] : -1, fix, rc);
-        if (agg2 != nullptr) restrict32<1>(ri, act ? agg2[i] : -1, fix, rc2);
+        restrict_q<1>(ri, act ? agg[i] : -1, fix, rc);
+        if (agg2 != nullptr) restrict_q<1>(ri, act ? agg2[i] : -1, fix, rc2);
     }
 }
 
@@ -561,7 +430,7 @@ __global__ void __launch_bounds__(RPB) cg2_restrict_kernel(int64_t r0, int64_t n
 template <bool START>
 __global__ void __launch_bounds__(256) cg2_convert_kernel(Scal *sc, Cg2 cg, long long *rc_fix, long long *rc_fix2) {
     if (!START && sc->done) return;
-    const double scale = sqrt(fmax(sc->rr, 1e-300)) / CO_RFIX32;
+    const double scale = sqrt(fmax(sc->rr, 1e-300)) / Q_STEPS;
     for (int j = blockIdx.x * 256 + threadIdx.x; j < cg.nc; j += gridDim.x * 256) {
         cg.rc[j] = (double)rc_fix[j] * scale;
         rc_fix[j] = 0;

@@ -117,6 +117,7 @@ __device__ __forceinline__ double2 ld2(const double *p) { return *reinterpret_ca
 __device__ __forceinline__ void st2(double *p, double a, double b) { *reinterpret_cast<double2 *>(p) = make_double2(a, b); }
 #include "pdn_peer_prim.cuh"
 #include "pdn_spmv.cuh"
+#include "pdn_cg2_tail.cuh"
 #include "pdn_sell.cuh"
 #include "pdn_coarse.cuh"
 #include "pdn_cg2.cuh"

@@ -126,6 +126,31 @@ __device__ __forceinline__ void special_rows(const SellOp &A, const double *__re
     }
 }
 
+// override rows (constraint terminals) for CG2: as special_rows, plus the restriction of their w entries
+__device__ __forceinline__ void special_rows_cg2(const SellOp &A, const double *__restrict__ x, double *__restrict__ y,
+                                                 const double *__restrict__ aux0, double (&acc)[3], int32_t gwarp,
+                                                 int32_t n_gwarp, const Cg2 &cg, double fix) {
+    const int lane = threadIdx.x & 31;
+    for (int32_t t = gwarp; t < A.n_special; t += n_gwarp) {
+        const int32_t row = A.sp_row[t];
+        if (row < A.row_begin || row >= A.row_end) continue;
+        double s2 = 0.0;
+        for (int32_t q = A.sp_rp[t] + lane; q < A.sp_rp[t + 1]; q += 32) s2 = fma(A.sp_va[q], x[A.sp_ci[q]], s2);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        if (lane == 0) {
+            row_epilogue<CG>(row, s2, x[row], aux0[row], y, acc);
+            const long long q = quantise(s2, fix);
+            const int32_t a = cg.agg[row];
+            if (a >= 0 && q != 0) red_add_u64(cg.tab + (size_t)a * TAB_STRIDE, (unsigned long long)(long long)q);
+            if (cg.nc2 > 0) {
+                const int32_t a2 = cg.agg2[row];
+                if (a2 >= 0 && q != 0) red_add_u64(cg.tab2 + (size_t)a2 * TAB_STRIDE, (unsigned long long)(long long)q);
+            }
+        }
+    }
+}
+
 template <int MODE, bool DIST>
 __global__ void __launch_bounds__(SELL_BLK, PDN_SELL_MINB) sell_spmv_kernel(SellOp A, const double *__restrict__ x,
                                                                double *__restrict__ y,
@@ -249,17 +274,21 @@ constexpr int ST_SLOT_ENT = ST_WCAP * SELL_C;
 constexpr int ST_SLOT_BYTES = ST_SLOT_ENT * 12;
 constexpr size_t ST_SMEM = (size_t)ST_WARPS * ST_NSLOT * ST_SLOT_BYTES + (size_t)ST_WARPS * ST_NSLOT * 8 + 3 * ST_WARPS * 8;
 
+// MODE == CG2 (round-2 PCG iteration, pdn_cg2.cuh): CG plus the restriction of w into cg.tab / cg.tab2 and the
+// recurrence tail (pdn_cg2_tail.cuh); the other modes ignore cg.
 template <int MODE, bool DIST>
 __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp A, const double *__restrict__ x,
                                                                      double *__restrict__ y,
                                                                      const double *__restrict__ aux0, Scal *sc,
-                                                                     double *partials, const PeerLink *Lp) {
+                                                                     double *partials, const PeerLink *Lp, Cg2 cg) {
     extern __shared__ __align__(128) unsigned char st_smem[];
+    constexpr int EMODE = MODE == CG2 ? CG : MODE;
     pdl_trigger();
     pdl_wait();
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }
+    const double fix = MODE == CG2 ? restrict_fix(sc) : 0.0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #if PDN_SELL_EVICT
     const uint64_t l2pol = tma::policy_evict_first();
@@ -327,9 +356,14 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         const int64_t row = sl * SELL_C + lane;
         const bool live = row < A.row_end && !((mask >> lane) & 1u);
         double xi = 0.0, ai = 0.0;
+        int32_t a1 = -1, a2 = -1;
         if (live) {
-            if (MODE == CG) xi = x[row];
-            if (MODE != PLAIN) ai = aux0[row];
+            if (EMODE == CG) xi = x[row];
+            if (EMODE != PLAIN) ai = aux0[row];
+            if (MODE == CG2) {
+                a1 = __ldg(cg.agg + row);
+                if (cg.nc2 > 0) a2 = __ldg(cg.agg2 + row);
+            }
         }
         const int w = (off1 - off) >> 5;
         double sum = 0.0;
@@ -366,7 +400,7 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
                 for (int i = 0; i < SELL_U; i++) sum = fma(v[i], xx[i], sum);
             }
         }
-        if (live) row_epilogue<MODE>(row, sum, xi, ai, y, acc);
+        if (live) row_epilogue<EMODE>(row, sum, xi, ai, y, acc);
         // every lane has consumed its words of slot j % NSLOT: refill it with slice j + NSLOT
         __syncwarp();
         if (jn < nj) {
@@ -374,13 +408,20 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
             issue(jn);
             jn++;
         }
+        if (MODE == CG2) {        // after the refill: the restriction runs while the next copies fly
+            restrict_q(sum, a1, fix, cg.tab);
+            if (cg.nc2 > 0) restrict_q(sum, a2, fix, cg.tab2);
+        }
     }
     __syncthreads();
-    special_rows<MODE>(A, x, y, aux0, acc, (int32_t)((blockIdx.x * ST_BLK + threadIdx.x) >> 5),
-                       (int32_t)((gridDim.x * ST_BLK) >> 5));
+    const int32_t gwarp = (int32_t)((blockIdx.x * ST_BLK + threadIdx.x) >> 5), n_gwarp = (int32_t)((gridDim.x * ST_BLK) >> 5);
+    if (MODE == CG2) special_rows_cg2(A, x, y, aux0, acc, gwarp, n_gwarp, cg, fix);
+    else special_rows<EMODE>(A, x, y, aux0, acc, gwarp, n_gwarp);
     if (MODE == PLAIN) return;
+    if (MODE == CG2) __threadfence();      // this thread's table atomics before the CTA's ticket
     if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-    dots_tail<MODE, DIST>(acc, sc, Lp);
+    if (MODE == CG2) cg2_tail<DIST>(acc, sc, cg, Lp, fix);
+    else dots_tail<EMODE, DIST>(acc, sc, Lp);
 }
 
 // ------------------------------------------------------------------------------------------------
