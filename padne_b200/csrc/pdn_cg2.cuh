@@ -226,21 +226,25 @@ __global__ void __launch_bounds__(256) band_hist_kernel(SellOp A, int64_t s0, in
 }
 
 // ---- K2 ---------------------------------------------------------------------------------------------------
-// x_c = A_c^-1 r_c from the fp32 copy of the inverse; CTA b owns CO_RB rows, the CTAs from grid1 on work on the
-// rank-local level.  The matrix loads are issued before the programmatic-launch wait (setup data).
-__global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(int32_t nc, const float *__restrict__ Ainv,
-                                                               const Scal *__restrict__ sc, const double *__restrict__ rc,
-                                                               double *__restrict__ xc, int grid1, int32_t nc2,
-                                                               const float *__restrict__ Ainv2,
-                                                               const double *__restrict__ rc2, double *__restrict__ xc2) {
+// RECUR: first the coarse-residual recurrence with the c_w table K1 just filled,
+//     c_s' = c_w + beta c_s,   r_c' = r_c - alpha c_s'          (P^T applied to s and r, pdn_cg2_tail.cuh)
+// computed by EVERY CTA into shared memory (3 nc independent loads per CTA instead of nc; as a loop of K1's last
+// CTA it cost 3-6 us); the first CTA of each level also stores c_s', r_c' into the slot of this iteration (the
+// others still read the previous slot: no race).  !RECUR (start / restart): r_c as the restriction kernel left it.
+// Then x_c = A_c^-1 r_c' from the fp32 copy of the inverse; CTA b owns CO_RB rows, the CTAs from grid1 on work on
+// the rank-local level.  The matrix loads are issued before the programmatic-launch wait (setup data).
+template <bool RECUR>
+__global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(const Scal *__restrict__ sc, Cg2 cg, const float *__restrict__ Ainv,
+                                                               double *__restrict__ xc, int grid1,
+                                                               const float *__restrict__ Ainv2, double *__restrict__ xc2,
+                                                               int summed) {
     __shared__ double rcd[CO_MAX];
     __shared__ double red[CO_RB][CO_BLK / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int row0 = blockIdx.x * CO_RB;
-    if ((int)blockIdx.x >= grid1) {
-        row0 = ((int)blockIdx.x - grid1) * CO_RB;
-        nc = nc2; Ainv = Ainv2; rc = rc2; xc = xc2;
-    }
+    const bool lvl2 = (int)blockIdx.x >= grid1;
+    const int row0 = (lvl2 ? (int)blockIdx.x - grid1 : (int)blockIdx.x) * CO_RB;
+    const int32_t nc = lvl2 ? cg.nc2 : cg.nc;
+    if (lvl2) { Ainv = Ainv2; xc = xc2; }
     float a[CO_RB][CO_JMAX];
 #pragma unroll
     for (int q = 0; q < CO_RB; q++)
@@ -252,7 +256,36 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(int32_t nc, const
     pdl_trigger();
     pdl_wait();
     if (sc->done) return;
-    for (int j = tid; j < nc; j += CO_BLK) rcd[j] = __ldcg(&rc[j]);
+    double *rc = lvl2 ? cg.rc2 : cg.rc, *cs = lvl2 ? cg.cs2 : cg.cs;
+    const int out = sc->iter & 1, in = out ^ 1;
+    if (RECUR) {
+        const unsigned long long *tab = lvl2 ? cg.tab2 : cg.tab;
+        const double alpha = sc->alpha, beta = sc->beta, invfix = sc->cw_invfix;
+        const bool from_sum = summed && !lvl2;           // several GPUs: the global level's c_w was summed by K1's tail
+        double cw[CO_JMAX], c0[CO_JMAX], r0[CO_JMAX];
+#pragma unroll
+        for (int t = 0; t < CO_JMAX; t++) {
+            const int j = tid + t * CO_BLK;
+            cw[t] = c0[t] = r0[t] = 0.0;
+            if (j < nc) {
+                cw[t] = from_sum ? __ldcg(cg.cw + j) : (double)(long long)__ldcg(tab + (size_t)j * TAB_STRIDE) * invfix;
+                c0[t] = __ldcg(cs + (size_t)in * nc + j);
+                r0[t] = __ldcg(rc + (size_t)in * nc + j);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < CO_JMAX; t++) {
+            const int j = tid + t * CO_BLK;
+            if (j < nc) {
+                const double c = cw[t] + beta * c0[t];
+                const double r = r0[t] - alpha * c;
+                rcd[j] = r;
+                if (row0 == 0) { cs[(size_t)out * nc + j] = c; rc[(size_t)out * nc + j] = r; }
+            }
+        }
+    } else {
+        for (int j = tid; j < nc; j += CO_BLK) rcd[j] = __ldcg(rc + (size_t)out * nc + j);
+    }
     __syncthreads();
     double acc[CO_RB];
 #pragma unroll
@@ -288,11 +321,18 @@ __global__ void __launch_bounds__(BLK) cg_update2_kernel(int64_t r0, int64_t n, 
                                                          const int32_t *__restrict__ agg, const double *__restrict__ xc,
                                                          const int32_t *__restrict__ agg2, const double *__restrict__ xc2,
                                                          const PeerLink *Lp, const HaloSend *hsp, size_t vec_off,
-                                                         const int32_t *__restrict__ send_idx, unsigned int *ticket) {
+                                                         const int32_t *__restrict__ send_idx, unsigned int *ticket,
+                                                         unsigned long long *tab, int32_t nc, unsigned long long *tab2,
+                                                         int32_t nc2) {
     pdl_trigger();
     pdl_wait();
     if (sc->done) return;
     if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 7);
+    // K2 has consumed the c_w tables of this iteration: clear them for the next K1 (spread over the grid)
+    if (!ZONLY) {
+        for (int j = blockIdx.x * BLK + threadIdx.x; j < nc; j += gridDim.x * BLK) tab[(size_t)j * TAB_STRIDE] = 0ull;
+        for (int j = blockIdx.x * BLK + threadIdx.x; j < nc2; j += gridDim.x * BLK) tab2[(size_t)j * TAB_STRIDE] = 0ull;
+    }
     const double alpha = sc->alpha, beta = sc->beta;
     const int64_t npair = (n - r0 + 1) >> 1;
     double zm = 0.0;
@@ -431,15 +471,16 @@ template <bool START>
 __global__ void __launch_bounds__(256) cg2_convert_kernel(Scal *sc, Cg2 cg, long long *rc_fix, long long *rc_fix2) {
     if (!START && sc->done) return;
     const double scale = sqrt(fmax(sc->rr, 1e-300)) / Q_STEPS;
+    const size_t slot = (size_t)(sc->iter & 1);       // the slot the next K2 reads (iter advances in K1's tail)
     for (int j = blockIdx.x * 256 + threadIdx.x; j < cg.nc; j += gridDim.x * 256) {
-        cg.rc[j] = (double)rc_fix[j] * scale;
+        cg.rc[slot * cg.nc + j] = (double)rc_fix[j] * scale;
         rc_fix[j] = 0;
-        if (START) { cg.cs[j] = 0.0; cg.tab[(size_t)j * TAB_STRIDE] = 0ull; }
+        if (START) { cg.cs[slot * cg.nc + j] = 0.0; cg.tab[(size_t)j * TAB_STRIDE] = 0ull; }
     }
     for (int j = blockIdx.x * 256 + threadIdx.x; j < cg.nc2; j += gridDim.x * 256) {
-        cg.rc2[j] = (double)rc_fix2[j] * scale;
+        cg.rc2[slot * cg.nc2 + j] = (double)rc_fix2[j] * scale;
         rc_fix2[j] = 0;
-        if (START) { cg.cs2[j] = 0.0; cg.tab2[(size_t)j * TAB_STRIDE] = 0ull; }
+        if (START) { cg.cs2[slot * cg.nc2 + j] = 0.0; cg.tab2[(size_t)j * TAB_STRIDE] = 0ull; }
     }
     if (START && blockIdx.x == 0 && threadIdx.x == 0) { sc->zmax_bits[0] = 0ull; sc->zmax_bits[1] = 0ull; }
 }

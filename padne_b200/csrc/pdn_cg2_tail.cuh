@@ -19,9 +19,14 @@ struct Cg2 {
     const int32_t *agg;               // [n] global-level aggregate of every row (-1: none)
     const int32_t *agg2;              // rank-local level (null without one)
     unsigned long long *tab, *tab2;   // [nc * TAB_STRIDE] fixed-point accumulators of c_w (zero between launches)
-    double *rc, *cs;                  // [nc] coarse residual P^T r and P^T s
+    double *rc, *cs;                  // [2][nc] coarse residual P^T r and P^T s, two slots (iteration parity):
+                                      // K2 reads slot (iter & 1) ^ 1 and writes slot iter & 1 (pdn_cg2.cuh)
     double *rc2, *cs2;                // the same for the rank-local level
+    double *cw;                       // [nc] several GPUs: c_w summed over the ranks by K1's tail (else unused)
     int32_t nc, nc2;
+    // per-CTA shared-memory windows of the restriction (sell_tma_kernel<CG2>): first aggregate of the window of
+    // every CTA, per level (setup: agg_min_kernel with the SpMV's own grid and slice split)
+    const int32_t *amin, *amin2;
 };
 
 __device__ __forceinline__ void red_add_u64(unsigned long long *p, unsigned long long v) {
@@ -33,6 +38,40 @@ __device__ __forceinline__ long long quantise(double val, double fix) {
     const double lim = (double)Q_LIM;
     return __double2ll_rn(q > lim ? lim : (q < -lim ? -lim : q));      // NaN -> 0 (cvt.rni.s64.f64 of NaN is 0)
 }
+// Per-CTA restriction table in shared memory.  A CTA's contiguous rows touch a short, contiguous range of
+// aggregates (bins are numbered mesh by mesh, row by row), so it accumulates c_w for the TABW aggregates from
+// amin[cta] on in shared memory and flushes the non-zero ones with one global atomic each at the end; an aggregate
+// outside the window (unstructured numbering) goes straight to the global table.  64-bit shared atomics are a CAS
+// loop on sm_100a (ATOMS.CAST.SPIN.64) and a 32-row slice holds 3.5 distinct aggregates on these meshes (rows of
+// valence 4 and 8 alternate and the length sort separates them), so neither 64-bit atomics nor warp collectives
+// per group pay; the 42-bit value goes in as THREE 14-bit limbs with native 32-bit ATOMS.ADD -- no collective, no
+// loop, the bank-conflict hardware serialises equal addresses.  2^17 entries per CTA and aggregate cannot overflow.
+constexpr int CO_MAX_TAIL = PDN_CO_MAX;   // pdn_common.cuh: largest coarse space
+constexpr int TABW = 512;
+constexpr size_t TAB_SMEM = (size_t)2 * 3 * TABW * sizeof(int);      // two levels
+
+__device__ __forceinline__ void restrict_smem(double val, int32_t a, double fix, int32_t amin, int *t /*[3][TABW]*/,
+                                              unsigned long long *gtab) {
+    if (a < 0) return;
+    const long long q = quantise(val, fix);
+    if (q == 0) return;
+    const unsigned d = (unsigned)(a - amin);
+    if (d < (unsigned)TABW) {
+        atomicAdd(&t[d], (int)(q & 0x3fff));
+        atomicAdd(&t[TABW + d], (int)((q >> 14) & 0x3fff));
+        atomicAdd(&t[2 * TABW + d], (int)(q >> 28));
+    } else {
+        red_add_u64(gtab + (size_t)a * TAB_STRIDE, (unsigned long long)q);
+    }
+}
+// all threads of the CTA, after a barrier: non-zero window entries -> the global table
+__device__ __forceinline__ void flush_smem_table(const int *t, int32_t amin, int32_t nc, unsigned long long *gtab) {
+    for (int d = threadIdx.x; d < TABW && amin + d < nc; d += blockDim.x) {
+        const long long sum = ((long long)t[2 * TABW + d] << 28) + ((long long)t[TABW + d] << 14) + (long long)t[d];
+        if (sum != 0) red_add_u64(gtab + (size_t)(amin + d) * TAB_STRIDE, (unsigned long long)sum);
+    }
+}
+
 // tab[a] += val over the lanes of a warp (all 32 lanes call, converged; a < 0 contributes nothing).  One pass per
 // DISTINCT aggregate in the warp -- 32 consecutive rows of a mesh sit in one or two bins -- each pass: the leader's
 // aggregate by shuffle, its members by ballot, the 42-bit fixed-point values of the members summed with two
@@ -112,29 +151,29 @@ __device__ __forceinline__ void cg2_tail(double (&acc)[3], Scal *sc, const Cg2 &
     }
     __syncthreads();
     if (sh_done) return;                        // identical on every rank; the host clears the tables before a restart
-    const double alpha = sh[0], beta = sh[1];
-    for (int j = tid; j < cg.nc; j += nt) {
-        double cw;
-        if (DIST && Lp != nullptr) {
-            cw = 0.0;
-            for (int r = 0; r < Lp->world; r++) {
-                const volatile long long *s = src + (size_t)r * PA_RC_SLOT;
-                cw += (double)s[4 + j] * reinterpret_cast<const volatile double *>(s)[3];
+    // The recurrence c_s = c_w + beta c_s, r_c -= alpha c_s itself runs in K2 (coarse_apply2_kernel), every CTA
+    // redundantly and in parallel: as a loop of this ONE CTA it made the tail 3-6 us long (measured: SpMV 33.4 us
+    // with it, 30.5 us without, 27.3 us with the plain dots tail).  Here only what K2 cannot know: 1/fix of this
+    // launch and, on several GPUs, c_w summed over the ranks in rank order.
+    if (tid == 0) sc->cw_invfix = invfix;
+    if (DIST && Lp != nullptr) {
+        constexpr int TU = (CO_MAX_TAIL + 383) / 384;
+        for (int j0 = tid; j0 < cg.nc; j0 += TU * nt) {
+            double cw[TU];
+#pragma unroll
+            for (int u = 0; u < TU; u++) {
+                const int j = j0 + u * nt;
+                cw[u] = 0.0;
+                if (j < cg.nc)
+                    for (int r = 0; r < Lp->world; r++) {
+                        const volatile long long *q = src + (size_t)r * PA_RC_SLOT;
+                        cw[u] += (double)q[4 + j] * reinterpret_cast<const volatile double *>(q)[3];
+                    }
             }
-        } else {
-            cw = (double)(long long)__ldcg(cg.tab + (size_t)j * TAB_STRIDE) * invfix;
+#pragma unroll
+            for (int u = 0; u < TU; u++)
+                if (j0 + u * nt < cg.nc) cg.cw[j0 + u * nt] = cw[u];
         }
-        cg.tab[(size_t)j * TAB_STRIDE] = 0ull;
-        const double c = cw + beta * cg.cs[j];
-        cg.cs[j] = c;
-        cg.rc[j] -= alpha * c;
-    }
-    for (int j = tid; j < cg.nc2; j += nt) {    // rank-local level: block diagonal, nothing to exchange
-        const double cw = (double)(long long)__ldcg(cg.tab2 + (size_t)j * TAB_STRIDE) * invfix;
-        cg.tab2[(size_t)j * TAB_STRIDE] = 0ull;
-        const double c = cw + beta * cg.cs2[j];
-        cg.cs2[j] = c;
-        cg.rc2[j] -= alpha * c;
     }
 }
 

@@ -34,6 +34,7 @@ struct Scal {
     // round-2 PCG iteration (pdn_cg2.cuh)
     unsigned long long zmax_bits[2];   // bits of max|z_i| over this rank's rows, slot = iteration parity
     double amax;                       // largest diagonal of the reduced operator (restriction scale, residual floor)
+    double cw_invfix;                  // 1 / fixed-point scale of the c_w table the last K1 filled
 };
 
 // CG2: CG with the restriction of w and the coarse-residual recurrence in the tail (pdn_cg2.cuh)

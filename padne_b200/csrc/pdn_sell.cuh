@@ -284,12 +284,21 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
     extern __shared__ __align__(128) unsigned char st_smem[];
     constexpr int EMODE = MODE == CG2 ? CG : MODE;
     pdl_trigger();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // CG2: restriction windows behind the ring (pdn_cg2_tail.cuh); cleared before the programmatic-launch wait
+    int *rtab = reinterpret_cast<int *>(st_smem + ST_SMEM);
+    int32_t amin1 = 0, amin2 = 0;
+    if (MODE == CG2) {
+        for (int e = threadIdx.x; e < (int)(TAB_SMEM / sizeof(int)); e += ST_BLK) rtab[e] = 0;
+        amin1 = __ldg(cg.amin + blockIdx.x);
+        if (cg.nc2 > 0) amin2 = __ldg(cg.amin2 + blockIdx.x);
+        __syncthreads();
+    }
     pdl_wait();
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }
     const double fix = MODE == CG2 ? restrict_fix(sc) : 0.0;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #if PDN_SELL_EVICT
     const uint64_t l2pol = tma::policy_evict_first();
 #endif
@@ -360,10 +369,12 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         if (live) {
             if (EMODE == CG) xi = x[row];
             if (EMODE != PLAIN) ai = aux0[row];
+#ifndef PDN_DBG_NO_AGGLOAD
             if (MODE == CG2) {
                 a1 = __ldg(cg.agg + row);
                 if (cg.nc2 > 0) a2 = __ldg(cg.agg2 + row);
             }
+#endif
         }
         const int w = (off1 - off) >> 5;
         double sum = 0.0;
@@ -408,20 +419,52 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
             issue(jn);
             jn++;
         }
+#ifndef PDN_DBG_NO_RESTRICT
         if (MODE == CG2) {        // after the refill: the restriction runs while the next copies fly
-            restrict_q(sum, a1, fix, cg.tab);
-            if (cg.nc2 > 0) restrict_q(sum, a2, fix, cg.tab2);
+            restrict_smem(sum, a1, fix, amin1, rtab, cg.tab);
+            if (cg.nc2 > 0) restrict_smem(sum, a2, fix, amin2, rtab + 3 * TABW, cg.tab2);
         }
+#endif
     }
     __syncthreads();
+    if (MODE == CG2) {
+        flush_smem_table(rtab, amin1, cg.nc, cg.tab);
+        if (cg.nc2 > 0) flush_smem_table(rtab + 3 * TABW, amin2, cg.nc2, cg.tab2);
+    }
     const int32_t gwarp = (int32_t)((blockIdx.x * ST_BLK + threadIdx.x) >> 5), n_gwarp = (int32_t)((gridDim.x * ST_BLK) >> 5);
     if (MODE == CG2) special_rows_cg2(A, x, y, aux0, acc, gwarp, n_gwarp, cg, fix);
     else special_rows<EMODE>(A, x, y, aux0, acc, gwarp, n_gwarp);
     if (MODE == PLAIN) return;
     if (MODE == CG2) __threadfence();      // this thread's table atomics before the CTA's ticket
     if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
+#ifdef PDN_DBG_PLAIN_TAIL
+    dots_tail<EMODE, DIST>(acc, sc, Lp);
+#else
     if (MODE == CG2) cg2_tail<DIST>(acc, sc, cg, Lp, fix);
     else dots_tail<EMODE, DIST>(acc, sc, Lp);
+#endif
+}
+
+// first aggregate of the restriction window of every CTA of sell_tma_kernel<CG2>: launched with THAT kernel's grid,
+// same static slice split; the smallest aggregate id among the CTA's rows (0 if it has none)
+__global__ void __launch_bounds__(256) agg_min_kernel(int64_t row_begin, int64_t row_end, const int32_t *__restrict__ agg,
+                                                      int32_t *__restrict__ amin) {
+    __shared__ int sm;
+    if (threadIdx.x == 0) sm = 0x7fffffff;
+    __syncthreads();
+    const int64_t s_begin = row_begin / SELL_C, s_end = (row_end + SELL_C - 1) / SELL_C;
+    const int64_t s_cnt = s_end - s_begin;
+    const int64_t s_lo = s_begin + (int64_t)blockIdx.x * s_cnt / gridDim.x;
+    const int64_t s_hi = s_begin + (int64_t)(blockIdx.x + 1) * s_cnt / gridDim.x;
+    int m = 0x7fffffff;
+    for (int64_t r = s_lo * SELL_C + threadIdx.x; r < s_hi * SELL_C && r < row_end; r += 256) {
+        const int32_t a = agg[r];
+        if (a >= 0 && a < m) m = a;
+    }
+    m = __reduce_min_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0) atomicMin(&sm, m);
+    __syncthreads();
+    if (threadIdx.x == 0) amin[blockIdx.x] = sm == 0x7fffffff ? 0 : sm;
 }
 
 // ------------------------------------------------------------------------------------------------

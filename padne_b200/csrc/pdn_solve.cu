@@ -189,7 +189,8 @@ struct SolveWork {
     int xs_per_sm = 0;
     double xs_coverage = 0.0;  // fraction of this rank's stored entries whose column falls inside the staged window
     DevBuf<unsigned long long> tab, tab2, band_hist;
-    DevBuf<double> rc_d, cs_d, rc2_d, cs2_d;
+    DevBuf<int32_t> cta_amin, cta_amin2;   // first aggregate of every SpMV CTA's restriction window, per level
+    DevBuf<double> rc_d, cs_d, rc2_d, cs2_d, cw_d;   // [2][nc] slots by iteration parity; cw: rank-summed c_w
     double amax = 0.0;         // largest diagonal of the reduced operator
     // vectors
     DevBuf<double> b, x, r, z, p, s, w, rhat, vv, sh, ph, tt, full_a, full_b, rhs_dev;
@@ -272,21 +273,36 @@ static const PeerLink *peer_link_or_none(pdn_ctx *ctx) {
     return nullptr;
 }
 
+// CTAs of the TMA-ring kernel: resident CTAs of THIS instantiation (CG2 carries its restriction windows in shared
+// memory), capped by the work
 template <int MODE, bool DIST>
-static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux, const Cg2 &cg = Cg2{}) {
-    const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+static int ring_grid(pdn_ctx *ctx, int64_t slices) {
 #if PDN_SELL_TMA
-    auto kern = sell_tma_kernel<MODE, DIST>;
+    constexpr size_t smem = ST_SMEM + (MODE == CG2 ? TAB_SMEM : 0);
     static int per_sm = 0;
     if (!per_sm) {
-        PDN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ST_SMEM));
-        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, ST_BLK, ST_SMEM));
+        PDN_CUDA(cudaFuncSetAttribute(sell_tma_kernel<MODE, DIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PDN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sell_tma_kernel<MODE, DIST>, ST_BLK, smem));
         if (per_sm < 1) per_sm = 1;
     }
     int64_t grid = std::min<int64_t>((int64_t)ctx->n_sm * per_sm, MAX_PART);
     grid = std::min<int64_t>(grid, std::max<int64_t>(1, (slices + ST_WARPS - 1) / ST_WARPS));
-    PDN_LAUNCH_PDL(ctx, w->pdl, kern, (int)grid, ST_BLK, ST_SMEM, w->A, x, y, aux, w->d_sc, w->partials.p, peer_link_or_none(ctx), cg);
+    return (int)grid;
 #else
+    return 1;
+#endif
+}
+
+template <int MODE, bool DIST>
+static void launch_sell_kernel(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux, const Cg2 &cg = Cg2{}) {
+    const int64_t slices = (w->A.row_end - w->A.row_begin + SELL_C - 1) / SELL_C;
+#if PDN_SELL_TMA
+    constexpr size_t smem = ST_SMEM + (MODE == CG2 ? TAB_SMEM : 0);
+    const int grid = ring_grid<MODE, DIST>(ctx, slices);
+    PDN_LAUNCH_PDL(ctx, w->pdl, (sell_tma_kernel<MODE, DIST>), grid, ST_BLK, smem, w->A, x, y, aux,
+                   w->d_sc, w->partials.p, peer_link_or_none(ctx), cg);
+#else
+    static_assert(MODE != CG2, "the direct-load kernel has no CG2 mode");
     auto kern = sell_spmv_kernel<MODE, DIST>;
     static int per_sm = 0;
     if (!per_sm) {
@@ -310,8 +326,11 @@ static Cg2 make_cg2(SolveWork *w) {
     cg.cs = w->cs_d.p;
     cg.rc2 = w->rc2_d.p;
     cg.cs2 = w->cs2_d.p;
+    cg.cw = w->cw_d.p;
     cg.nc = w->nc;
     cg.nc2 = w->nc2;
+    cg.amin = w->cta_amin.p;
+    cg.amin2 = w->cta_amin2.p;
     return cg;
 }
 
@@ -762,10 +781,11 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
 }
 
 // ---- round-2 PCG iteration (pdn_cg2.cuh): K1 SpMV + restriction + recurrence, K2 coarse apply, K3 update + z ----
-static void launch_coarse_apply2(pdn_ctx *ctx, SolveWork *w) {
+template <bool RECUR>
+static void launch_coarse_apply2(pdn_ctx *ctx, SolveWork *w, bool summed) {
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB, cgrid2 = (w->nc2 + CO_RB - 1) / CO_RB;
-    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply2_kernel, cgrid + cgrid2, CO_BLK, 0, w->nc, w->co_Af.p, w->d_sc, w->rc_d.p, w->xc.p,
-                   cgrid, w->nc2, w->co_Af2.p, w->rc2_d.p, w->xc2.p);
+    PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply2_kernel<RECUR>, cgrid + cgrid2, CO_BLK, 0, w->d_sc, make_cg2(w), w->co_Af.p, w->xc.p,
+                   cgrid, w->co_Af2.p, w->xc2.p, summed ? 1 : 0);
 }
 
 template <bool ZONLY>
@@ -782,11 +802,13 @@ static void launch_update2(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));
         PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<1024, ZONLY>), zgrid, 1024, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
                        w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, pdn_peer_link_dev(ctx), w->halo.peer_d.p,
-                       pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx));
+                       pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx), w->tab.p, w->nc, w->tab2.p,
+                       w->nc2);
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<RPB, ZONLY>), vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
                        w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, (const PeerLink *)nullptr,
-                       (const HaloSend *)nullptr, (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr);
+                       (const HaloSend *)nullptr, (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr, w->tab.p, w->nc,
+                       w->tab2.p, w->nc2);
     }
 }
 
@@ -815,7 +837,7 @@ void enqueue_pcg2_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         if (is_dist(ctx)) launch_sell_kernel<CG2, true>(ctx, w, w->z.p, w->w.p, w->r.p, cg);
         else launch_sell_kernel<CG2, false>(ctx, w, w->z.p, w->w.p, w->r.p, cg);
     }
-    launch_coarse_apply2(ctx, w);
+    launch_coarse_apply2<true>(ctx, w, is_dist(ctx));
     launch_update2<false>(ctx, w, vgrid);
 }
 
@@ -825,7 +847,7 @@ void enqueue_pcg2_start(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     PDN_CUDA(cudaMemsetAsync(w->rc_fix.p, 0, (size_t)2 * w->nc * sizeof(long long), st));
     if (w->nc2 > 0) PDN_CUDA(cudaMemsetAsync(w->rc_fix2.p, 0, (size_t)2 * w->nc2 * sizeof(long long), st));
     enqueue_pcg2_restrict<true>(ctx, w, vgrid);
-    launch_coarse_apply2(ctx, w);
+    launch_coarse_apply2<false>(ctx, w, false);
     launch_update2<true>(ctx, w, vgrid);
 }
 
@@ -1934,18 +1956,38 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             }
         }
     }
-    // round-2 iteration (three kernels, one exchange): PCG + two-level + the x-staging SpMV; with several GPUs it
-    // needs the peer-memory link (the NCCL fallback keeps the round-1 iteration).  PADNE_B200_PCG=v1 forces round 1.
+    // Round-2 iteration (three kernels, ONE exchange of dots + coarse sums per iteration, pdn_cg2.cuh): the default
+    // on several GPUs with the peer-memory link, where an exchange costs 6-14 us (the NCCL fallback keeps the
+    // round-1 iteration).  On ONE GPU it measures slower than the round-1 iteration at 1M rows (54 against 47.5 us
+    // per iteration: the restriction + tail cost the SpMV 6 us, and the fused update moves the same ~100 B per row
+    // through L2 as the two kernels it replaces), so it is opt-in there.  PADNE_B200_PCG=v1 / v2 forces either.
     {
         const char *e = getenv("PADNE_B200_PCG");
-        w->v2 = method == PDN_METHOD_PCG && w->two_level && (!is_dist(ctx) || pdn_peer_enabled(ctx)) &&
-                !(e && strcmp(e, "v1") == 0);
+        const bool can_v2 = method == PDN_METHOD_PCG && w->two_level && (!is_dist(ctx) || pdn_peer_enabled(ctx));
+        const bool want_v2 = e ? strcmp(e, "v2") == 0 : is_dist(ctx);
+        w->v2 = can_v2 && want_v2;
         if (w->v2) {
             w->tab.reserve((size_t)w->nc * TAB_STRIDE + 8);
             w->tab2.reserve((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8);
-            w->rc_d.reserve((size_t)w->nc + 8); w->cs_d.reserve((size_t)w->nc + 8);
-            w->rc2_d.reserve((size_t)std::max(w->nc2, 1) + 8); w->cs2_d.reserve((size_t)std::max(w->nc2, 1) + 8);
+            const size_t c1 = (size_t)2 * w->nc + 8, c2 = (size_t)2 * std::max(w->nc2, 1) + 8;
+            w->rc_d.reserve(c1); w->cs_d.reserve(c1); w->cw_d.reserve(c1);
+            w->rc2_d.reserve(c2); w->cs2_d.reserve(c2);
+            PDN_CUDA(cudaMemsetAsync(w->rc_d.p, 0, c1 * sizeof(double), st));
+            PDN_CUDA(cudaMemsetAsync(w->cs_d.p, 0, c1 * sizeof(double), st));
+            PDN_CUDA(cudaMemsetAsync(w->cw_d.p, 0, c1 * sizeof(double), st));
+            PDN_CUDA(cudaMemsetAsync(w->rc2_d.p, 0, c2 * sizeof(double), st));
+            PDN_CUDA(cudaMemsetAsync(w->cs2_d.p, 0, c2 * sizeof(double), st));
             if (w->nc2 == 0) { w->rc_fix2.reserve(8); w->xc2.reserve(8); w->co_Af2.reserve(8); }
+            // restriction windows of the ring kernel's CTAs (same grid, same slice split)
+            if (!w->xs) {
+                const int64_t slices = (w->row_end - w->row_begin + SELL_C - 1) / SELL_C;
+                const int rgrid = is_dist(ctx) ? ring_grid<CG2, true>(ctx, slices) : ring_grid<CG2, false>(ctx, slices);
+                w->cta_amin.reserve((size_t)rgrid + 8);
+                w->cta_amin2.reserve((size_t)rgrid + 8);
+                PDN_LAUNCH(ctx, agg_min_kernel, rgrid, 256, 0, w->row_begin, w->row_end, w->agg.p, w->cta_amin.p);
+                if (w->nc2 > 0)
+                    PDN_LAUNCH(ctx, agg_min_kernel, rgrid, 256, 0, w->row_begin, w->row_end, w->agg2.p, w->cta_amin2.p);
+            }
             PDN_CUDA(cudaMemsetAsync(w->tab.p, 0, ((size_t)w->nc * TAB_STRIDE + 8) * sizeof(unsigned long long), st));
             PDN_CUDA(cudaMemsetAsync(w->tab2.p, 0, ((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8) * sizeof(unsigned long long), st));
         }
@@ -2133,11 +2175,11 @@ void pdn_bench_spmv_impl(pdn_ctx *ctx, int32_t reps, int mode, double *ms) {
         launch();
         PDN_CUDA(cudaEventRecord(ev[2 * k + 1], st));
         if (mode == 2 && v2) {   // the rest of a round-2 iteration: K2, K3 (dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux)
-            launch_coarse_apply2(ctx, w);
+            launch_coarse_apply2<true>(ctx, w, false);
             PDN_LAUNCH(ctx, (cg_update2_kernel<RPB, false>), pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p,
                        v3.p, v4.p, v5.p, aux.p, w->agg.p, w->xc.p, w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr,
                        w->nc2 > 0 ? w->xc2.p : (const double *)nullptr, (const PeerLink *)nullptr, (const HaloSend *)nullptr,
-                       (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr);
+                       (size_t)0, (const int32_t *)nullptr, (unsigned int *)nullptr, w->tab.p, w->nc, w->tab2.p, w->nc2);
         } else if (mode == 2)   // dinv = v6, w = y, z = x, p = v3, s = v4, x = v5, r = aux
             PDN_LAUNCH(ctx, cg_update_kernel<false>, pdn_grid(ctx, r1 - r0, RPB, 8), RPB, 0, r0, r1, w->d_sc, v6.p, y.p, x.p,
                        v3.p, v4.p, v5.p, aux.p, (const int32_t *)nullptr, (long long *)nullptr, 0);
