@@ -245,7 +245,7 @@ def info_dict(info):
 class Workload:
     """One synthetic board on this rank: pinned host copies, device copies, and the two timed steps."""
 
-    def __init__(self, torch, capi, ctx, dev, config, n, skw):
+    def __init__(self, torch, capi, ctx, dev, config, n, skw, part=False):
         from padne_b200.stamps import build_stamps
         self.torch, self.ctx, self.config = torch, ctx, config
         fs = make_board(config, n).to_flat()
@@ -262,18 +262,20 @@ class Workload:
         self.h2d = int(sum(t.numel() * t.element_size() for t in self.pinned.values()))
         self.d2h = int(fs.N * 8)
         self.skw = dict(skw, n_nodes=fs.n_nodes)
+        # several GPUs: partitioned assembly -- every rank builds (and, in the e2e leg, uploads) only its rows' meshes
+        self.akw = dict(n_nodes=fs.n_nodes) if part else {}
 
     def step_device(self):
         d, fs = self.devt, self.fs
         nnz = self.ctx.assemble(d["v_off"], d["xy"], d["t_off"], d["tri"], d["cond"], fs.N, d["s_row"], d["s_col"],
-                                d["s_val"], d["s_op"])
+                                d["s_val"], d["s_op"], **self.akw)
         _, info = self.ctx.solve(d["rhs"], out=self.v_dev, **self.skw)
         return nnz, info
 
     def step_host(self):
         p, fs = self.pinned_np, self.fs
         nnz = self.ctx.assemble(p["v_off"], p["xy"], p["t_off"], p["tri"], p["cond"], fs.N, p["s_row"], p["s_col"],
-                                p["s_val"], p["s_op"])
+                                p["s_val"], p["s_op"], **self.akw)
         _, info = self.ctx.solve(p["rhs"], out=self.v_host_np, **self.skw)
         return nnz, info
 
@@ -298,6 +300,8 @@ def main():
     ap.add_argument("--atol", type=float, default=0.0, help="absolute bar on ||L v - r||; 0 = the reference's 1e-9, <0 = off")
     ap.add_argument("--precond", default="auto", choices=["auto", "jacobi", "two-level"])
     ap.add_argument("--n-coarse", type=int, default=0)
+    ap.add_argument("--replicated-assembly", action="store_true",
+                    help="several GPUs: every rank assembles the whole board (round-1 behaviour) instead of its own rows")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "padne_b200" else args.warmup
 
@@ -376,7 +380,8 @@ def main():
         return float(total.item()), outs, launches
 
     # ---- the headline workload ---------------------------------------------------------------------
-    wl = Workload(torch, capi, ctx, dev, args.config, args.n, skw)
+    part_asm = partitioned and not args.replicated_assembly
+    wl = Workload(torch, capi, ctx, dev, args.config, args.n, skw, part=part_asm)
     fs = wl.fs
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -389,11 +394,16 @@ def main():
     # ---- dominant kernel: SpMV with fused dots (and, round-2 iteration, the restriction), in situ ---------
     n_red = fs.n_nodes
     indptr_tail = ctx.get_csr()[0]
-    nnz_nodes = int(indptr_tail[n_red])
+    if part_asm:
+        # the resident CSR holds this rank's rows (+ a few terminals): its node entries ARE the launch's share
+        nnz_nodes = int(indptr_tail[n_red])
+        alg_bytes = 12.0 * nnz_nodes + 20.0 * (n_red / world)
+    else:
+        nnz_nodes = int(indptr_tail[n_red])
+        alg_bytes = 12.0 * nnz_nodes + 20.0 * n_red      # 12 B/nnz + 20 B/row
+        if partitioned:
+            alg_bytes /= world                           # the timed launch covers this rank's rows only
     del indptr_tail
-    alg_bytes = 12.0 * nnz_nodes + 20.0 * n_red          # 12 B/nnz + 20 B/row
-    if partitioned:
-        alg_bytes /= world                               # the timed launch covers this rank's rows only
     spmv_ms = ctx.bench_spmv(reps=200, mode=2)
     spmv_ms_warm = ctx.bench_spmv(reps=200, mode=0)
     spmv_ms_cold = ctx.bench_spmv(reps=50, mode=1)
@@ -413,7 +423,7 @@ def main():
         del wl.devt, wl.pinned, wl.pinned_np        # ~0.4 GB per GPU back before the 10M board arrives
         torch.cuda.empty_cache()
         # config 4: the 8-layer 300x300 mm backplane, ~10M DOF, strong-scaled over the ranks of this run
-        w4 = Workload(torch, capi, ctx, dev, "8layer_10M", None, skw)
+        w4 = Workload(torch, capi, ctx, dev, "8layer_10M", None, skw, part=part_asm)
         t4, o4, _ = timed(ctx, w4.step_device, args.named_steps, 2, True)
         i4 = o4[-1][1]
         named["8layer_10M"] = dict(info_dict(i4), dof=w4.fs.N, n_gpus=world, scaling="strong" if world > 1 else "single GPU",
@@ -460,7 +470,8 @@ def main():
                         "atol": args.atol if args.atol != 0 else 1e-9}, **info_dict(info),
                        parallelism=("single GPU" if world == 1 else
                                     f"one board row-partitioned over {world} GPUs (one peer-memory exchange of dots + coarse "
-                                    f"sums and one halo exchange per iteration over NVLink, NCCL for setup; assembly replicated)"
+                                    f"sums and one halo exchange per iteration over NVLink, NCCL for setup; "
+                                    f"{'assembly and setup partitioned by rows' if part_asm else 'assembly replicated'})"
                                     if partitioned else f"{world} independent boards, one per GPU"),
                        l2="256 MiB written between timed steps; per-step working set exceeds the 126 MB L2"),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,

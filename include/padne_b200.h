@@ -141,6 +141,19 @@ int pdn_assemble(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const doubl
                  int64_t n_stamp, const int32_t *s_row, const int32_t *s_col, const double *s_val,
                  const int32_t *s_op, int on_device, int64_t *nnz_out);
 
+/* The same on a context with a communicator (pdn_comm_init), PARTITIONED: the matrix is block diagonal per mesh
+ * (padne/solver.py:216-229, 563-575) and the coupling is the stamp list, so every rank builds only the rows of its
+ * range of the solve's row partition (contiguous 1024-row windows of the n_nodes voltage rows, split evenly), the
+ * extra rows (>= n_nodes) and the few constraint-terminal rows, and -- from host inputs -- uploads only the meshes
+ * those rows live in.  All ranks pass the SAME full arrays; the resident system holds this rank's rows only
+ * (pdn_get_csr returns them, the other rows empty; *nnz_out is the local count) and pdn_solve works from that,
+ * exchanging what the setup needs (row permutation, halo marks, coarse matrix).  Without a communicator it is
+ * pdn_assemble. */
+int pdn_assemble_part(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
+                      const int64_t *t_off, const int32_t *tri, const double *conductance, int64_t N,
+                      int64_t n_nodes, int64_t n_stamp, const int32_t *s_row, const int32_t *s_col,
+                      const double *s_val, const int32_t *s_op, int on_device, int64_t *nnz_out);
+
 /* Copy the resident CSR out (L.tocsr(): int32 sorted indices, no explicit zeros).
  * indptr [N+1], indices [nnz], data [nnz].  Any pointer may be NULL to skip that array. */
 int pdn_get_csr(pdn_ctx *ctx, int32_t *indptr, int32_t *indices, double *data, int on_device);

@@ -25,7 +25,7 @@ METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 
 # every symbol include/padne_b200.h declares (tests check that the library exports them all)
 SYMBOLS = ("pdn_create", "pdn_destroy", "pdn_strerror", "pdn_last_error", "pdn_launch_count",
-           "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_get_csr", "pdn_get_shape",
+           "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_assemble_part", "pdn_get_csr", "pdn_get_shape",
            "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density",
            "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info", "pdn_nearest_vertex",
            "pdn_format_f64", "pdn_vtu_piece_bound", "pdn_vtu_piece")
@@ -110,6 +110,7 @@ def load_library(path: str | None = None):
     lib.pdn_stream.restype = ctypes.c_uint64
     lib.pdn_element_weights.argtypes = [P, I64, P, I64, P, P, ctypes.c_int]
     lib.pdn_assemble.argtypes = [P, I32, P, P, P, P, P, I64, I64, P, P, P, P, ctypes.c_int, ctypes.POINTER(I64)]
+    lib.pdn_assemble_part.argtypes = [P, I32, P, P, P, P, P, I64, I64, I64, P, P, P, P, ctypes.c_int, ctypes.POINTER(I64)]
     lib.pdn_get_csr.argtypes = [P, P, P, P, ctypes.c_int]
     lib.pdn_get_shape.argtypes = [P, ctypes.POINTER(I64), ctypes.POINTER(I64)]
     lib.pdn_set_csr.argtypes = [P, I64, I64, P, P, P, ctypes.c_int]
@@ -258,10 +259,12 @@ class Context:
         return w
 
     # -- kernels (1)+(2) -----------------------------------------------------------------------------
-    def assemble(self, v_off, xy, t_off, tri, conductance, N, s_row, s_col, s_val, s_op) -> int:
+    def assemble(self, v_off, xy, t_off, tri, conductance, N, s_row, s_col, s_val, s_op, n_nodes=None) -> int:
         """``assemble_system`` (``padne/solver.py:783-812``); the CSR stays resident.  Returns nnz.
 
-        All arrays host (numpy) or all device (torch cuda tensors)."""
+        All arrays host (numpy) or all device (torch cuda tensors).  ``n_nodes`` (voltage rows) on a context
+        with a communicator: partitioned assembly -- this rank builds (and, from host arrays, uploads) only its
+        share (``pdn_assemble_part``)."""
         # whatever was resident is about to be replaced: solver.solve_system must not mistake it for an earlier
         # ResidentSystem (solver.assemble_flat sets the new token afterwards)
         self._resident_token = None
@@ -273,6 +276,12 @@ class Context:
             s_row, s_col, s_op = _np(s_row, np.int32), _np(s_col, np.int32), _np(s_op, np.int32)
             s_val = _np(s_val, np.float64)
         nnz = ctypes.c_int64()
+        if n_nodes is not None:
+            st = self._lib.pdn_assemble_part(self._ctx, int(conductance.shape[0]), _ptr(v_off), _ptr(xy), _ptr(t_off),
+                                             _ptr(tri), _ptr(conductance), int(N), int(n_nodes), int(s_row.shape[0]),
+                                             _ptr(s_row), _ptr(s_col), _ptr(s_val), _ptr(s_op), int(dev), ctypes.byref(nnz))
+            self._check(st, "assemble_part")
+            return int(nnz.value)
         st = self._lib.pdn_assemble(self._ctx, int(conductance.shape[0]), _ptr(v_off), _ptr(xy), _ptr(t_off),
                                     _ptr(tri), _ptr(conductance), int(N), int(s_row.shape[0]), _ptr(s_row),
                                     _ptr(s_col), _ptr(s_val), _ptr(s_op), int(dev), ctypes.byref(nnz))

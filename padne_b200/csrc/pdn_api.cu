@@ -229,6 +229,21 @@ int pdn_assemble(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const doubl
     });
 }
 
+int pdn_assemble_part(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy, const int64_t *t_off,
+                      const int32_t *tri, const double *conductance, int64_t N, int64_t n_nodes, int64_t n_stamp,
+                      const int32_t *s_row, const int32_t *s_col, const double *s_val, const int32_t *s_op,
+                      int on_device, int64_t *nnz_out) {
+    return pdn_guard(ctx, [&] {
+        if (n_mesh < 0 || N <= 0 || n_stamp < 0 || !v_off || !t_off || n_nodes <= 0 || n_nodes > N)
+            PDN_FAIL(PDN_EINVAL, "assemble_part: bad sizes");
+        if (n_stamp > 0 && (!s_row || !s_col || !s_val || !s_op)) PDN_FAIL(PDN_EINVAL, "assemble_part: stamp arrays missing");
+        ctx->L.valid = false;
+        ctx->geo_valid = false;
+        pdn_assemble_impl(ctx, n_mesh, v_off, xy, t_off, tri, conductance, N, n_stamp, s_row, s_col, s_val,
+                          s_op, on_device != 0, nnz_out, n_nodes);
+    });
+}
+
 int pdn_get_shape(pdn_ctx *ctx, int64_t *N, int64_t *nnz) {
     if (!ctx) return PDN_EINVAL;
     if (!ctx->L.valid) return PDN_ENOSYSTEM;

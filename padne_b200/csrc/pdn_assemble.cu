@@ -87,9 +87,15 @@ __global__ void __launch_bounds__(BLK) element_kernel(int n_mesh, const int64_t 
                                                       const double2 *__restrict__ xy,
                                                       const int32_t *__restrict__ tri, int64_t n_t,
                                                       double *__restrict__ w, int32_t *__restrict__ gtri,
-                                                      int32_t *__restrict__ cnt, int32_t *status) {
+                                                      int32_t *__restrict__ cnt, int32_t *status,
+                                                      const int32_t *__restrict__ mesh_needed) {
     for (int64_t t = (int64_t)blockIdx.x * BLK + threadIdx.x; t < n_t; t += (int64_t)gridDim.x * BLK) {
         const int m = n_mesh > 1 ? find_segment(t_off, n_mesh, t) : 0;
+        if (mesh_needed != nullptr && !mesh_needed[m]) {     // partitioned assembly: this mesh is not resident here
+#pragma unroll
+            for (int c = 0; c < 3; c++) gtri[3 * t + c] = -1;
+            continue;
+        }
         const int64_t vo = v_off[m], nv = v_off[m + 1] - vo;
         int32_t v[3] = {tri[3 * t], tri[3 * t + 1], tri[3 * t + 2]};
         bool ok = true;
@@ -130,10 +136,37 @@ __global__ void __launch_bounds__(BLK) stamp_count_kernel(int64_t n_stamp, int64
 // row capacity = neighbours (<= incident triangles + 1) + diagonal + stamps
 __global__ void __launch_bounds__(BLK) capacity_kernel(int64_t N, const int32_t *__restrict__ cnt,
                                                        const int32_t *__restrict__ cnt_s,
-                                                       int32_t *__restrict__ ub) {
+                                                       int32_t *__restrict__ ub, const uint8_t *__restrict__ want) {
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < N; i += (int64_t)gridDim.x * BLK) {
         int32_t c = cnt[i];
-        ub[i] = (c > 0 ? c + 2 : 0) + cnt_s[i];
+        ub[i] = (want == nullptr || want[i]) ? (c > 0 ? c + 2 : 0) + cnt_s[i] : 0;
+    }
+}
+
+// ---- partitioned assembly (several GPUs): which rows this rank builds -------------------------------------------
+// want[i] = 1 for the rows of this rank's range, for the extra rows (constraints: i >= n_nodes), and -- second kernel --
+// for every constraint TERMINAL: both ends of any stamp that touches an extra row or column (voltage-source /
+// regulator / ground terminals and regulator sense nodes, padne/solver.py:503-538, 558-560).  The solve eliminates
+// the constraints on the host of EVERY rank, so those few rows are built everywhere; need[m] flags their meshes.
+__global__ void __launch_bounds__(BLK) want_range_kernel(int64_t N, int64_t lo, int64_t hi, int64_t n_nodes,
+                                                         uint8_t *__restrict__ want) {
+    for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < N; i += (int64_t)gridDim.x * BLK)
+        want[i] = ((i >= lo && i < hi) || i >= n_nodes) ? 1 : 0;
+}
+__global__ void __launch_bounds__(BLK) want_terminal_kernel(int64_t n_stamp, int64_t N, int64_t n_nodes, int64_t n_v,
+                                                            int n_mesh, const int64_t *__restrict__ v_off,
+                                                            const int32_t *__restrict__ s_row,
+                                                            const int32_t *__restrict__ s_col, uint8_t *__restrict__ want,
+                                                            int32_t *__restrict__ need) {
+    for (int64_t s = (int64_t)blockIdx.x * BLK + threadIdx.x; s < n_stamp; s += (int64_t)gridDim.x * BLK) {
+        const int32_t r = s_row[s], c = s_col[s];
+        if (r < 0 || r >= N || c < 0 || c >= N) continue;           // reported by stamp_count_kernel
+        if (r < n_nodes && c < n_nodes) continue;
+        const int32_t e[2] = {r, c};
+        for (int k = 0; k < 2; k++) {
+            want[e[k]] = 1;
+            if (e[k] < n_v) need[n_mesh > 1 ? find_segment(v_off, n_mesh, e[k]) : 0] = 1;
+        }
     }
 }
 
@@ -222,8 +255,10 @@ __global__ void __launch_bounds__(BLK) row_kernel(
     const int32_t *__restrict__ inc_ptr, const int32_t *__restrict__ inc,
     const int32_t *__restrict__ sinc_ptr, int32_t *__restrict__ sinc, const int32_t *__restrict__ s_col,
     const double *__restrict__ s_val, const int32_t *__restrict__ s_op, const int32_t *__restrict__ ub_ptr,
-    int32_t *__restrict__ tcol, double *__restrict__ tval, int32_t *__restrict__ row_len, int32_t *status) {
+    int32_t *__restrict__ tcol, double *__restrict__ tval, int32_t *__restrict__ row_len, int32_t *status,
+    const uint8_t *__restrict__ want) {
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < N; i += (int64_t)gridDim.x * BLK) {
+        if (want != nullptr && !want[i]) { row_len[i] = 0; continue; }      // another rank's row
         RowBuf row;
         row.col = tcol + ub_ptr[i];
         row.val = tval + ub_ptr[i];
@@ -543,6 +578,8 @@ struct AssembleWork {
     DevIn<int32_t> d_tri, d_srow, d_scol, d_sop;
     DevBuf<double> w, tval;
     DevBuf<int32_t> gtri, cnt, cnt_s, ub, inc_ptr, sinc_ptr, ub_ptr, inc, sinc, tcol, row_len;
+    DevBuf<uint8_t> want;          // partitioned assembly: rows this rank builds
+    DevBuf<int32_t> mesh_needed;   // ... and the meshes it needs resident
 };
 
 void pdn_assemble_release(pdn_ctx *ctx) {
@@ -553,8 +590,24 @@ void pdn_assemble_release(pdn_ctx *ctx) {
 void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
                        const int64_t *t_off, const int32_t *tri, const double *conductance, int64_t N,
                        int64_t n_stamp, const int32_t *s_row, const int32_t *s_col, const double *s_val,
-                       const int32_t *s_op, bool on_device, int64_t *nnz_out) {
+                       const int32_t *s_op, bool on_device, int64_t *nnz_out, int64_t n_nodes_part) {
     cudaStream_t st = ctx->stream;
+    // Partitioned assembly (n_nodes_part >= 0 on a context with a communicator): this rank builds the rows of its
+    // range of the row partition (pdn_row_partition: the one the solve uses), the extra rows and the constraint
+    // terminals; from HOST inputs only the meshes those rows live in are uploaded.  Everything else of the resident
+    // system stays empty -- the matrix is block diagonal per mesh (padne/solver.py:216-229, 563-575) and the
+    // coupling is the stamp list, so no rank needs another rank's rows.
+    const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
+    const bool part = n_nodes_part >= 0 && world > 1;
+    int64_t part_lo = 0, part_hi = N;
+    if (part) {
+        if (n_nodes_part > N) PDN_FAIL(PDN_EINVAL, "assemble: n_nodes larger than N");
+        std::vector<int64_t> begin(world + 1);
+        pdn_row_partition(n_nodes_part, world, begin.data());
+        part_lo = begin[me];
+        part_hi = begin[me + 1];
+    }
+    ctx->part_valid = false;
     // offsets are needed on both sides; they are tiny
     std::vector<int64_t> h_voff(n_mesh + 1), h_toff(n_mesh + 1);
     if (on_device) {
@@ -584,13 +637,54 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     DevIn<int32_t> &d_tri = aw.d_tri, &d_srow = aw.d_srow, &d_scol = aw.d_scol, &d_sop = aw.d_sop;
     d_voff.set(v_off, n_mesh + 1, on_device, st);
     d_toff.set(t_off, n_mesh + 1, on_device, st);
-    d_xy.set(xy, (size_t)n_v * 2, on_device, st);
-    d_tri.set(tri, (size_t)n_t * 3, on_device, st);
     d_cond.set(conductance, n_mesh, on_device, st);
     d_srow.set(s_row, n_stamp, on_device, st);
     d_scol.set(s_col, n_stamp, on_device, st);
     d_sval.set(s_val, n_stamp, on_device, st);
     d_sop.set(s_op, n_stamp, on_device, st);
+    const uint8_t *want = nullptr;
+    const int32_t *mesh_needed = nullptr;
+    std::vector<int32_t> h_need(n_mesh > 0 ? n_mesh : 1, 1);
+    if (part) {
+        aw.want.reserve((size_t)N);
+        aw.mesh_needed.reserve((size_t)n_mesh + 1);
+        PDN_CUDA(cudaMemsetAsync(aw.mesh_needed.p, 0, ((size_t)n_mesh + 1) * sizeof(int32_t), st));
+        PDN_LAUNCH(ctx, want_range_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, N, part_lo, part_hi, n_nodes_part, aw.want.p);
+        if (n_stamp > 0)
+            PDN_LAUNCH(ctx, want_terminal_kernel, pdn_grid(ctx, n_stamp, BLK, 8), BLK, 0, n_stamp, N, n_nodes_part, n_v,
+                       (int)n_mesh, d_voff.p, d_srow.p, d_scol.p, aw.want.p, aw.mesh_needed.p);
+        if (n_mesh > 0) {
+            PDN_CUDA(cudaMemcpyAsync(h_need.data(), aw.mesh_needed.p, n_mesh * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            PDN_CUDA(cudaStreamSynchronize(st));
+            for (int m = 0; m < n_mesh; m++)
+                if (h_voff[m] < part_hi && h_voff[m + 1] > part_lo) h_need[m] = 1;      // overlaps this rank's rows
+            PDN_CUDA(cudaMemcpyAsync(aw.mesh_needed.p, h_need.data(), n_mesh * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        }
+        want = aw.want.p;
+        mesh_needed = aw.mesh_needed.p;
+    }
+    if (on_device || !part) {
+        d_xy.set(xy, (size_t)n_v * 2, on_device, st);
+        d_tri.set(tri, (size_t)n_t * 3, on_device, st);
+    } else {
+        // host inputs, partitioned: full-size device arrays (the kernels index them globally), only the needed
+        // meshes copied in -- consecutive needed meshes as one copy
+        d_xy.own.reserve((size_t)n_v * 2);
+        d_tri.own.reserve((size_t)n_t * 3);
+        d_xy.p = d_xy.own.p;
+        d_tri.p = d_tri.own.p;
+        for (int m = 0; m < n_mesh;) {
+            if (!h_need[m]) { m++; continue; }
+            int m1 = m;
+            while (m1 + 1 < n_mesh && h_need[m1 + 1]) m1++;
+            const int64_t v0 = h_voff[m], v1 = h_voff[m1 + 1], t0 = h_toff[m], t1 = h_toff[m1 + 1];
+            if (v1 > v0)
+                PDN_CUDA(cudaMemcpyAsync(d_xy.own.p + 2 * v0, xy + 2 * v0, (size_t)(v1 - v0) * 2 * sizeof(double), cudaMemcpyHostToDevice, st));
+            if (t1 > t0)
+                PDN_CUDA(cudaMemcpyAsync(d_tri.own.p + 3 * t0, tri + 3 * t0, (size_t)(t1 - t0) * 3 * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+            m = m1 + 1;
+        }
+    }
 
     DevBuf<double> &w = aw.w, &tval = aw.tval;
     DevBuf<int32_t> &gtri = aw.gtri, &cnt = aw.cnt, &cnt_s = aw.cnt_s, &ub = aw.ub, &inc_ptr = aw.inc_ptr,
@@ -616,11 +710,11 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     PDN_CUDA(cudaMemsetAsync(cnt_s.p, 0, (size_t)N * sizeof(int32_t), st));
     if (n_t > 0)
         PDN_LAUNCH(ctx, element_kernel, pdn_grid(ctx, n_t, BLK, 8), BLK, 0, (int)n_mesh, d_voff.p, d_toff.p,
-                   (const double2 *)d_xy.p, d_tri.p, n_t, w.p, gtri.p, cnt.p, ctx->d_status);
+                   (const double2 *)d_xy.p, d_tri.p, n_t, w.p, gtri.p, cnt.p, ctx->d_status, mesh_needed);
     if (n_stamp > 0)
         PDN_LAUNCH(ctx, stamp_count_kernel, pdn_grid(ctx, n_stamp, BLK, 8), BLK, 0, n_stamp, N, d_srow.p,
                    d_scol.p, cnt_s.p, ctx->d_status);
-    PDN_LAUNCH(ctx, capacity_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, N, cnt.p, cnt_s.p, ub.p);
+    PDN_LAUNCH(ctx, capacity_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, N, cnt.p, cnt_s.p, ub.p, want);
     pdn_exclusive_scan_i32(ctx, cnt.p, N, inc_ptr.p);
     pdn_exclusive_scan_i32(ctx, cnt_s.p, N, sinc_ptr.p);
     pdn_exclusive_scan_i32(ctx, ub.p, N, ub_ptr.p);
@@ -632,7 +726,7 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
                    cnt.p, inc.p, n_stamp, N, d_srow.p, d_scol.p, sinc_ptr.p, cnt_s.p, sinc.p);
     PDN_LAUNCH(ctx, row_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, N, n_v, (int)n_mesh, d_voff.p, d_cond.p,
                gtri.p, w.p, inc_ptr.p, inc.p, sinc_ptr.p, sinc.p, d_scol.p, d_sval.p, d_sop.p, ub_ptr.p,
-               tcol.p, tval.p, row_len.p, ctx->d_status);
+               tcol.p, tval.p, row_len.p, ctx->d_status, want);
 
     CsrDev &L = ctx->L;
     L.indptr.reserve((size_t)N + 1);
@@ -649,6 +743,12 @@ void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const
     L.n = N;
     L.nnz = nnz;
     L.valid = true;
+    if (part) {
+        ctx->part_valid = true;
+        ctx->part_lo = part_lo;
+        ctx->part_hi = part_hi;
+        ctx->part_n_nodes = n_nodes_part;
+    }
     // keep the geometry for the solve's coarse space (pdn_coarse.cuh)
     if (n_v > 0 && n_mesh > 0) {
         if (on_device) {   // borrowed pointers: take copies

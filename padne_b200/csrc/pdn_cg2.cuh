@@ -86,6 +86,10 @@ __global__ void __launch_bounds__(SX_BLK, 2) sell_xs_kernel(SellOp A, XsPlan P, 
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }
+    if (MODE == CG2 && DIST && Lp != nullptr && cg.halo != nullptr) {     // the peers' interface entries of x
+        peer_halo_wait(*Lp, *cg.halo);
+        __syncthreads();
+    }
     const double fix = MODE == CG2 ? restrict_fix(sc) : 0.0;
     double acc[3] = {0.0, 0.0, 0.0};
 
@@ -237,7 +241,7 @@ template <bool RECUR>
 __global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(const Scal *__restrict__ sc, Cg2 cg, const float *__restrict__ Ainv,
                                                                double *__restrict__ xc, int grid1,
                                                                const float *__restrict__ Ainv2, double *__restrict__ xc2,
-                                                               int summed) {
+                                                               int summed, const PeerLink *Lp) {
     __shared__ double rcd[CO_MAX];
     __shared__ double red[CO_RB][CO_BLK / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -256,6 +260,7 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(const Scal *__res
     pdl_trigger();
     pdl_wait();
     if (sc->done) return;
+    if (Lp != nullptr && blockIdx.x == 0 && tid == 0) peer_log(*Lp, 2);      // event log: K2 start (PADNE_B200_PEER_STATS)
     double *rc = lvl2 ? cg.rc2 : cg.rc, *cs = lvl2 ? cg.cs2 : cg.cs;
     const int out = sc->iter & 1, in = out ^ 1;
     if (RECUR) {
@@ -306,6 +311,7 @@ __global__ void __launch_bounds__(CO_BLK) coarse_apply2_kernel(const Scal *__res
         for (int k = 0; k < CO_BLK / 32; k++) sum += red[tid][k];
         xc[row0 + tid] = sum;
     }
+    if (Lp != nullptr && blockIdx.x == 0 && tid == 0) peer_log(*Lp, 3);      // K2's first CTA done
 }
 
 // ---- K3 ---------------------------------------------------------------------------------------------------
@@ -436,7 +442,7 @@ __global__ void __launch_bounds__(BLK) cg_update2_kernel(int64_t r0, int64_t n, 
                 if (g[u] >= 0) dst[g[u]] = v[u];
         }
     }
-    peer_halo_tail(L, hs);
+    peer_halo_post(L, hs);      // the wait is K1's (peer_halo_wait, pdn_peer_prim.cuh)
 }
 
 // ---- start / resync -------------------------------------------------------------------------------------------

@@ -27,6 +27,11 @@ struct Cg2 {
     // per-CTA shared-memory windows of the restriction (sell_tma_kernel<CG2>): first aggregate of the window of
     // every CTA, per level (setup: agg_min_kernel with the SpMV's own grid and slice split)
     const int32_t *amin, *amin2;
+    // several GPUs, halo fused into K3: the plan (recv_cnt) K1 waits on before it reads z; else null
+    const HaloSend *halo;
+    // several GPUs: [first, last] aggregate this rank's rows touch (agg_range_kernel; first > last: none).  Only that
+    // range of c_w crosses NVLink: a rank that owns 2 of 16 layers touches 1/8 of the aggregates.
+    const int32_t *arange;
 };
 
 __device__ __forceinline__ void red_add_u64(unsigned long long *p, unsigned long long v) {
@@ -118,10 +123,26 @@ __device__ __forceinline__ void cg2_tail(double (&acc)[3], Scal *sc, const Cg2 &
         const size_t slot = (size_t)(e & 1) * PEER_MAX;
         if (tid == 0) { peer_log(L, 0); sh[0] = acc[0]; sh[1] = acc[1]; sh[2] = acc[2]; sh[3] = invfix; sh_ok = 1; }
         __syncthreads();
-        for (int k = 0; k < L.world; k++) {
-            long long *dst = reinterpret_cast<long long *>(L.arena[k] + PA_CW_VAL) + (slot + L.me) * PA_RC_SLOT;
-            if (tid < 4) reinterpret_cast<double *>(dst)[tid] = sh[tid];
-            for (int j = tid; j < cg.nc; j += nt) dst[4 + j] = (long long)__ldcg(cg.tab + (size_t)j * TAB_STRIDE);
+        // slot layout: 8 header words [gamma, delta, rr, 1/fix, first aggregate, count, -, -], then q[first .. first + count)
+        const int32_t alo = __ldg(cg.arange), ahi = __ldg(cg.arange + 1);
+        const int32_t acnt = ahi >= alo ? ahi - alo + 1 : 0;
+        {   // this rank's range of the table once into registers, then one store per peer (remote stores are fire-and-forget)
+            constexpr int TU = (CO_MAX_TAIL + 383) / 384;
+            long long q[TU];
+#pragma unroll
+            for (int u = 0; u < TU; u++) {
+                const int j = tid + u * nt;
+                q[u] = j < acnt ? (long long)__ldcg(cg.tab + (size_t)(alo + j) * TAB_STRIDE) : 0;
+            }
+            for (int k = 0; k < L.world; k++) {
+                long long *dst = reinterpret_cast<long long *>(L.arena[k] + PA_CW_VAL) + (slot + L.me) * PA_RC_SLOT;
+                if (tid < 4) reinterpret_cast<double *>(dst)[tid] = sh[tid];
+                if (tid == 4) dst[4] = alo;
+                if (tid == 5) dst[5] = acnt;
+#pragma unroll
+                for (int u = 0; u < TU; u++)
+                    if (tid + u * nt < acnt) dst[8 + tid + u * nt] = q[u];
+            }
         }
         __threadfence_system();
         __syncthreads();
@@ -129,6 +150,36 @@ __device__ __forceinline__ void cg2_tail(double (&acc)[3], Scal *sc, const Cg2 &
         if (tid < L.world && !peer_wait(L.arena[L.me] + PA_CW_FLAG + slot + tid, e, L.status, L.epoch + 5)) sh_ok = 0;
         __syncthreads();
         src = reinterpret_cast<const volatile long long *>(L.arena[L.me] + PA_CW_VAL) + slot * PA_RC_SLOT;
+        {   // c_w summed over the ranks in rank order, for K2.  The acquire of the waiting threads and the barrier order
+            // these loads after the peers' stores; ld.cg reads L2, where the remote stores land (no L1 copy can be
+            // stale).  All loads of a thread are independent: as volatile loads in a loop this took ~10 us on 2 GPUs.
+            const long long *sl = const_cast<const long long *>(src);
+            double inv[PEER_MAX];
+            int lo[PEER_MAX], cnt[PEER_MAX];
+#pragma unroll
+            for (int r = 0; r < PEER_MAX; r++) {
+                const long long *h = sl + (size_t)r * PA_RC_SLOT;
+                inv[r] = r < L.world ? __ldcg(reinterpret_cast<const double *>(h) + 3) : 0.0;
+                lo[r] = r < L.world ? (int)__ldcg(h + 4) : 0;
+                cnt[r] = r < L.world ? (int)__ldcg(h + 5) : 0;
+            }
+#pragma unroll 1
+            for (int j = tid; j < cg.nc; j += 2 * nt) {          // two entries x PEER_MAX independent loads in flight
+                const int j2 = j + nt;
+                long long va[PEER_MAX], vb[PEER_MAX];
+#pragma unroll
+                for (int r = 0; r < PEER_MAX; r++) {
+                    const unsigned da = (unsigned)(j - lo[r]), db = (unsigned)(j2 - lo[r]);
+                    va[r] = da < (unsigned)cnt[r] ? __ldcg(sl + (size_t)r * PA_RC_SLOT + 8 + da) : 0;
+                    vb[r] = (db < (unsigned)cnt[r] && j2 < cg.nc) ? __ldcg(sl + (size_t)r * PA_RC_SLOT + 8 + db) : 0;
+                }
+                double ca = 0.0, cb = 0.0;
+#pragma unroll
+                for (int r = 0; r < PEER_MAX; r++) { ca += (double)va[r] * inv[r]; cb += (double)vb[r] * inv[r]; }
+                cg.cw[j] = ca;
+                if (j2 < cg.nc) cg.cw[j2] = cb;
+            }
+        }
         if (tid == 0) {
             L.epoch[7] = e;
             peer_log(L, 1);
@@ -156,24 +207,5 @@ __device__ __forceinline__ void cg2_tail(double (&acc)[3], Scal *sc, const Cg2 &
     // with it, 30.5 us without, 27.3 us with the plain dots tail).  Here only what K2 cannot know: 1/fix of this
     // launch and, on several GPUs, c_w summed over the ranks in rank order.
     if (tid == 0) sc->cw_invfix = invfix;
-    if (DIST && Lp != nullptr) {
-        constexpr int TU = (CO_MAX_TAIL + 383) / 384;
-        for (int j0 = tid; j0 < cg.nc; j0 += TU * nt) {
-            double cw[TU];
-#pragma unroll
-            for (int u = 0; u < TU; u++) {
-                const int j = j0 + u * nt;
-                cw[u] = 0.0;
-                if (j < cg.nc)
-                    for (int r = 0; r < Lp->world; r++) {
-                        const volatile long long *q = src + (size_t)r * PA_RC_SLOT;
-                        cw[u] += (double)q[4 + j] * reinterpret_cast<const volatile double *>(q)[3];
-                    }
-            }
-#pragma unroll
-            for (int u = 0; u < TU; u++)
-                if (j0 + u * nt < cg.nc) cg.cw[j0 + u * nt] = cw[u];
-        }
-    }
 }
 

@@ -101,6 +101,14 @@ __global__ void __launch_bounds__(CO_BLK) agg_raw_kernel(int64_t n, int64_t row_
     }
 }
 
+// occupancy of the raw bins from an (all-gathered) raw id array
+__global__ void __launch_bounds__(CO_BLK) agg_used_kernel(int64_t n, const int32_t *__restrict__ raw, int32_t *__restrict__ used) {
+    for (int64_t r = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; r < n; r += (int64_t)gridDim.x * CO_BLK) {
+        const int32_t a = raw[r];
+        if (a >= 0) used[a] = 1;
+    }
+}
+
 __global__ void __launch_bounds__(CO_BLK) agg_final_kernel(int64_t n, const int32_t *__restrict__ cid, int32_t *__restrict__ agg) {
     for (int64_t r = (int64_t)blockIdx.x * CO_BLK + threadIdx.x; r < n; r += (int64_t)gridDim.x * CO_BLK) {
         const int32_t a = agg[r];

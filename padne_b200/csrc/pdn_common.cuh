@@ -131,6 +131,10 @@ struct pdn_ctx {
     int64_t launches = 0;
     std::string last_error;
     CsrDev L;                  // the full system of padne/solver.py:783-812
+    // Partitioned assembly (pdn_assemble_part on a context with a communicator): only the rows [part_lo, part_hi),
+    // the constraint terminals and the extra rows of L are assembled on this rank; the other rows are empty.
+    bool part_valid = false;
+    int64_t part_lo = 0, part_hi = 0, part_n_nodes = 0;
     int32_t *d_status = nullptr;  // [4] device status words (error code, detail)
     int32_t *h_status = nullptr;  // pinned mirror
     DevBuf<char> l2_flush;
@@ -231,7 +235,8 @@ void pdn_flush_l2(pdn_ctx *ctx);
 void pdn_assemble_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const double *xy,
                        const int64_t *t_off, const int32_t *tri, const double *conductance,
                        int64_t N, int64_t n_stamp, const int32_t *s_row, const int32_t *s_col,
-                       const double *s_val, const int32_t *s_op, bool on_device, int64_t *nnz_out);
+                       const double *s_val, const int32_t *s_op, bool on_device, int64_t *nnz_out,
+                       int64_t n_nodes_part = -1);
 void pdn_element_weights_impl(pdn_ctx *ctx, int64_t n_v, const double *xy, int64_t n_t,
                               const int32_t *tri, double *w, bool on_device);
 void pdn_nearest_vertex_impl(pdn_ctx *ctx, int32_t n_mesh, const int64_t *v_off, const int32_t *mesh_layer,
@@ -287,6 +292,21 @@ int pdn_comm_world(const pdn_ctx *ctx);
 void pdn_comm_release(pdn_ctx *ctx);
 void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count);
 void pdn_comm_allreduce_sum_i64(pdn_ctx *ctx, long long *buf, int count);
+void pdn_comm_allreduce_max(pdn_ctx *ctx, double *buf, int count);
+void pdn_comm_allreduce_sum_i32(pdn_ctx *ctx, int32_t *buf, size_t count);
+void pdn_comm_allgatherv_i32(pdn_ctx *ctx, int32_t *vec, const int64_t *begin);
+
+// Row partition of a system with n node rows over `world` ranks: contiguous ranges of whole 1024-row sort windows
+// (pdn_sell.cuh), split evenly; begin has world + 1 entries.  Used by the partitioned assembly and by the solve.
+constexpr int64_t PDN_PART_WIN = 1024;
+static inline void pdn_row_partition(int64_t n, int world, int64_t *begin) {
+    const int64_t n_win = (n + PDN_PART_WIN - 1) / PDN_PART_WIN;
+    for (int k = 0; k <= world; k++) {
+        const int64_t b = (int64_t)k * n_win / world * PDN_PART_WIN;
+        begin[k] = b < n ? b : n;
+    }
+    begin[world] = n;
+}
 void pdn_comm_allgatherv(pdn_ctx *ctx, double *vec, const int64_t *begin);
 void pdn_comm_exchange(pdn_ctx *ctx, const double *sendbuf, const int32_t *send_off, const int32_t *send_cnt,
                        double *recvbuf, const int32_t *recv_off, const int32_t *recv_cnt);

@@ -21,6 +21,8 @@ typedef struct ncclComm *ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 constexpr int kNcclSuccess = 0;
 constexpr int kNcclSum = 0;
+constexpr int kNcclMax = 2;       // ncclMax
+constexpr int kNcclInt32 = 2;     // ncclInt32 / ncclInt
 constexpr int kNcclInt8 = 0;      // ncclInt8 / ncclChar
 constexpr int kNcclInt64 = 4;     // ncclInt64
 constexpr int kNcclFloat64 = 8;   // ncclFloat64
@@ -207,6 +209,28 @@ void pdn_comm_allreduce_sum(pdn_ctx *ctx, double *buf, int count) {
 // in-place sum of 64-bit integers (the fixed-point coarse residual: exact, order-independent)
 void pdn_comm_allreduce_sum_i64(pdn_ctx *ctx, long long *buf, int count) {
     PDN_NCCL(nccl().AllReduce(buf, buf, (size_t)count, kNcclInt64, kNcclSum, ctx->comm->comm, ctx->stream));
+}
+
+// in-place maximum of `count` doubles over the ranks
+void pdn_comm_allreduce_max(pdn_ctx *ctx, double *buf, int count) {
+    PDN_NCCL(nccl().AllReduce(buf, buf, (size_t)count, kNcclFloat64, kNcclMax, ctx->comm->comm, ctx->stream));
+}
+
+// in-place sum of 32-bit integers (halo marks: every rank sets its own bit, so the sum is the bitwise OR)
+void pdn_comm_allreduce_sum_i32(pdn_ctx *ctx, int32_t *buf, size_t count) {
+    PDN_NCCL(nccl().AllReduce(buf, buf, count, kNcclInt32, kNcclSum, ctx->comm->comm, ctx->stream));
+}
+
+// int32 vec[begin[k] .. begin[k+1]) is broadcast from rank k, for every k
+void pdn_comm_allgatherv_i32(pdn_ctx *ctx, int32_t *vec, const int64_t *begin) {
+    const int world = ctx->comm->world;
+    PDN_NCCL(nccl().GroupStart());
+    for (int k = 0; k < world; k++) {
+        const int64_t cnt = begin[k + 1] - begin[k];
+        if (cnt > 0)
+            PDN_NCCL(nccl().Broadcast(vec + begin[k], vec + begin[k], (size_t)cnt, kNcclInt32, k, ctx->comm->comm, ctx->stream));
+    }
+    PDN_NCCL(nccl().GroupEnd());
 }
 
 // vec[begin[k] .. begin[k+1]) is broadcast from rank k, for every k (an all-gather with ragged slices)

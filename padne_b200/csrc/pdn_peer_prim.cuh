@@ -127,3 +127,25 @@ __device__ __forceinline__ void peer_halo_tail(const PeerLink &L, const HaloSend
     __syncthreads();
     if (tid == 0) { L.epoch[0] = e; peer_log(L, 5); }
 }
+
+// ---- halo, consumer-side wait (round-2 iteration) ---------------------------------------------------------
+// peer_halo_post: the LAST CTA of the kernel that wrote the vector (all threads call) has stored this rank's
+// interface entries into the peers' copies: fence, raise the flags, advance the epoch -- and leave.  The wait moves
+// to the kernel that READS the vector (peer_halo_wait, first thing after its programmatic-launch wait, threads
+// < world of every CTA, followed by a CTA barrier): the flag round trip overlaps the kernel boundary and the
+// reader's prologue instead of sitting in the writer's tail (6 us per iteration on 2 GPUs).
+__device__ __forceinline__ void peer_halo_post(const PeerLink &L, const HaloSend &h) {
+    const int tid = threadIdx.x;
+    if (tid == 0) peer_log(L, 4);
+    __threadfence_system();
+    __syncthreads();
+    const unsigned long long e = L.epoch[0] + 1;
+    if (tid < L.world && tid != L.me && h.cnt[tid] > 0) st_release_sys(L.arena[tid] + PA_HALO_FLAG + L.me, e);
+    __syncthreads();
+    if (tid == 0) { L.epoch[0] = e; peer_log(L, 5); }
+}
+__device__ __forceinline__ void peer_halo_wait(const PeerLink &L, const HaloSend &h) {
+    const int tid = threadIdx.x;
+    if (tid < L.world && tid != L.me && h.recv_cnt[tid] > 0)
+        peer_wait(L.arena[L.me] + PA_HALO_FLAG + tid, L.epoch[0], L.status, L.epoch + 4);
+}

@@ -292,11 +292,15 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         for (int e = threadIdx.x; e < (int)(TAB_SMEM / sizeof(int)); e += ST_BLK) rtab[e] = 0;
         amin1 = __ldg(cg.amin + blockIdx.x);
         if (cg.nc2 > 0) amin2 = __ldg(cg.amin2 + blockIdx.x);
-        __syncthreads();
     }
     pdl_wait();
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
+    }
+    if (MODE == CG2) {
+        // several GPUs, halo fused into K3: wait here for the peers' interface entries of x (consumer-side wait)
+        if (DIST && Lp != nullptr && cg.halo != nullptr) peer_halo_wait(*Lp, *cg.halo);
+        __syncthreads();      // restriction windows cleared, halo entries in place
     }
     const double fix = MODE == CG2 ? restrict_fix(sc) : 0.0;
 #if PDN_SELL_EVICT
@@ -445,6 +449,22 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
 #endif
 }
 
+// [first, last] aggregate among the rows [row_begin, row_end): range[0] starts at INT_MAX, range[1] at -1
+__global__ void __launch_bounds__(256) agg_range_kernel(int64_t row_begin, int64_t row_end, const int32_t *__restrict__ agg,
+                                                        int32_t *range) {
+    int lo = 0x7fffffff, hi = -1;
+    for (int64_t r = row_begin + (int64_t)blockIdx.x * 256 + threadIdx.x; r < row_end; r += (int64_t)gridDim.x * 256) {
+        const int32_t a = agg[r];
+        if (a >= 0) { lo = a < lo ? a : lo; hi = a > hi ? a : hi; }
+    }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    if ((threadIdx.x & 31) == 0) {
+        if (lo != 0x7fffffff) atomicMin(&range[0], lo);
+        if (hi >= 0) atomicMax(&range[1], hi);
+    }
+}
+
 // first aggregate of the restriction window of every CTA of sell_tma_kernel<CG2>: launched with THAT kernel's grid,
 // same static slice split; the smallest aggregate id among the CTA's rows (0 if it has none)
 __global__ void __launch_bounds__(256) agg_min_kernel(int64_t row_begin, int64_t row_end, const int32_t *__restrict__ agg,
@@ -492,12 +512,13 @@ __global__ void __launch_bounds__(256) sell_len_kernel(int64_t n, int64_t n_pad,
 }
 
 // one CTA per window: stable sort by descending length (bitonic network on unique keys)
+// (win0: first window of the launch -- a partitioned setup sorts this rank's windows only)
 __global__ void __launch_bounds__(SELL_WIN) sell_sort_kernel(const int32_t *__restrict__ len,
                                                             int32_t *__restrict__ perm,
-                                                            int32_t *__restrict__ inv) {
+                                                            int32_t *__restrict__ inv, int64_t win0) {
     __shared__ uint32_t key[SELL_WIN];
     const int t = threadIdx.x;
-    const int64_t base = (int64_t)blockIdx.x * SELL_WIN;
+    const int64_t base = (win0 + (int64_t)blockIdx.x) * SELL_WIN;
     key[t] = ((uint32_t)(SELL_MAXLEN - len[base + t]) << 10) | (uint32_t)t;
     for (int k = 2; k <= SELL_WIN; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -536,11 +557,13 @@ __global__ void __launch_bounds__(256) sell_fill_kernel(int64_t n, int64_t n_sli
                                                         const int32_t *__restrict__ inv,
                                                         const int32_t *__restrict__ soff,
                                                         int32_t *__restrict__ o_ci, double *__restrict__ o_va,
-                                                        uint32_t *__restrict__ smask, double *__restrict__ dinv) {
+                                                        uint32_t *__restrict__ smask, double *__restrict__ dinv,
+                                                        int64_t s_first) {
+    // slices [s_first, n_slices): a partitioned setup fills this rank's slices only
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
     const int64_t n_warp = ((int64_t)gridDim.x * 256) >> 5;
-    for (int64_t s = warp; s < n_slices; s += n_warp) {
+    for (int64_t s = s_first + warp; s < n_slices; s += n_warp) {
         const int64_t r = s * SELL_C + lane;
         const int32_t off = soff[s], w = (soff[s + 1] - off) >> 5;
         const int64_t old = perm[r];

@@ -184,11 +184,14 @@ struct SolveWork {
     int local_level = 0;       // 0: not requested, 1: built, < 0: requested but not built (-PDN_E* / -100: see build_coarse)
     // round-2 PCG iteration (pdn_cg2.cuh): restriction tables of K1, coarse vectors kept by recurrence
     bool v2 = false;           // this solve runs the three-kernel iteration
+    bool part = false;         // several GPUs, partitioned assembly: the resident L holds this rank's rows (+ terminals, extras)
+    bool halo_fused = false;   // v2, several GPUs: K3's last CTA pushes the halo of z and K1 waits for the peers'
     bool xs = true;            // SpMV with x-band staging (else the round-1 TMA-ring kernel)
     XsPlan xsp{0, 1 << 28};
     int xs_per_sm = 0;
     double xs_coverage = 0.0;  // fraction of this rank's stored entries whose column falls inside the staged window
     DevBuf<unsigned long long> tab, tab2, band_hist;
+    DevBuf<int32_t> agg_range;             // [2] first / last aggregate of this rank's rows (exchange payload)
     DevBuf<int32_t> cta_amin, cta_amin2;   // first aggregate of every SpMV CTA's restriction window, per level
     DevBuf<double> rc_d, cs_d, rc2_d, cs2_d, cw_d;   // [2][nc] slots by iteration parity; cw: rank-summed c_w
     double amax = 0.0;         // largest diagonal of the reduced operator
@@ -331,6 +334,8 @@ static Cg2 make_cg2(SolveWork *w) {
     cg.nc2 = w->nc2;
     cg.amin = w->cta_amin.p;
     cg.amin2 = w->cta_amin2.p;
+    cg.halo = w->halo_fused ? w->halo.peer_d.p : nullptr;
+    cg.arange = w->agg_range.p;
     return cg;
 }
 
@@ -715,7 +720,8 @@ void restart_scal(pdn_ctx *ctx, SolveWork *w, double tol2) {
 static bool halo_in_coarse_z(pdn_ctx *ctx, SolveWork *w) {
     const char *e = getenv("PADNE_B200_HALO_FUSED");   // 0: keep the separate push / wait kernels (same on every rank)
     if (e && e[0] == '0') return false;
-    return w->two_level && is_dist(ctx) && pdn_peer_enabled(ctx) && w->halo.n_interface <= 32768;
+    // n_interface counts the interface rows of ALL ranks (every rank sees the same number: same decision)
+    return w->two_level && is_dist(ctx) && pdn_peer_enabled(ctx) && w->halo.n_interface <= 16384 * pdn_comm_world(ctx);
 }
 
 void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, double boost, const double *src,
@@ -785,7 +791,7 @@ template <bool RECUR>
 static void launch_coarse_apply2(pdn_ctx *ctx, SolveWork *w, bool summed) {
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB, cgrid2 = (w->nc2 + CO_RB - 1) / CO_RB;
     PDN_LAUNCH_PDL(ctx, w->pdl, coarse_apply2_kernel<RECUR>, cgrid + cgrid2, CO_BLK, 0, w->d_sc, make_cg2(w), w->co_Af.p, w->xc.p,
-                   cgrid, w->co_Af2.p, w->xc2.p, summed ? 1 : 0);
+                   cgrid, w->co_Af2.p, w->xc2.p, summed ? 1 : 0, summed ? peer_link_or_none(ctx) : (const PeerLink *)nullptr);
 }
 
 template <bool ZONLY>
@@ -918,8 +924,13 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, KrylovTarget tgt
     PDN_CUDA(cudaEventCreate(&ev1));
     PDN_CUDA(cudaEventRecord(ev0, st));
 
-    // ||b|| (b is replicated: no communication)
+    // ||b|| (b is replicated: no communication -- unless the assembly was partitioned: own rows, summed over the ranks)
     reset_scal(ctx, w, 0.0, 0.0, max_iter);
+    if (w->part) {
+        PDN_LAUNCH(ctx, sumsq_kernel<true>, vgrid, RPB, 0, r0, r1, w->b.p, (const double *)nullptr, w->d_sc, w->d_out,
+                   w->partials.p);
+        dist_reduce<7>(ctx, w);
+    } else
     PDN_LAUNCH(ctx, sumsq_kernel<false>, pdn_grid(ctx, n, RPB, 8), RPB, 0, (int64_t)0, n, w->b.p,
                (const double *)nullptr, w->d_sc, w->d_out, w->partials.p);
     double bnorm2 = 0.0;
@@ -1225,12 +1236,15 @@ struct RowPart {
     }
 };
 
+// what: bit 0 the SELL part, bit 1 the override rows.  (A partitioned setup marks its own SELL rows, sums the marks
+// over the ranks -- every rank sets only its own bit, so the sum is the OR -- and then adds the override rows,
+// which every rank holds.)
 __global__ void __launch_bounds__(256) halo_mark_kernel(SellOp A, int64_t n_slices, RowPart part,
-                                                        uint32_t *__restrict__ needmask) {
+                                                        uint32_t *__restrict__ needmask, int what) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
     const int64_t n_warp = ((int64_t)gridDim.x * 256) >> 5;
-    for (int64_t s = warp; s < n_slices; s += n_warp) {
+    for (int64_t s = warp; (what & 1) && s < n_slices; s += n_warp) {
         const int64_t r = s * SELL_C + lane;
         if (r >= A.n) continue;
         const int32_t off = A.soff[s], w = (A.soff[s + 1] - off) >> 5;
@@ -1242,7 +1256,7 @@ __global__ void __launch_bounds__(256) halo_mark_kernel(SellOp A, int64_t n_slic
         }
     }
     // override rows
-    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < A.n_special; t += (int64_t)gridDim.x * 256) {
+    for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; (what & 2) && t < A.n_special; t += (int64_t)gridDim.x * 256) {
         const int ko = part.owner(A.sp_row[t]);
         const int64_t lo = part.begin[ko], hi = part.begin[ko + 1];
         for (int32_t q = A.sp_rp[t]; q < A.sp_rp[t + 1]; q++) {
@@ -1310,8 +1324,16 @@ static void build_halo_plan(pdn_ctx *ctx, SolveWork *w, int32_t /*n_sp_entries*/
     for (int k = 0; k <= world; k++) part.begin[k] = h.begin[k];
     w->needmask.reserve((size_t)n);
     PDN_CUDA(cudaMemsetAsync(w->needmask.p, 0, (size_t)n * sizeof(uint32_t), st));
-    PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
-               w->needmask.p);
+    if (w->part) {
+        PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
+                   w->needmask.p, 1);
+        pdn_comm_allreduce_sum_i32(ctx, reinterpret_cast<int32_t *>(w->needmask.p), (size_t)n);
+        PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
+                   w->needmask.p, 2);
+    } else {
+        PDN_LAUNCH(ctx, halo_mark_kernel, pdn_grid(ctx, w->n_slices * 32, 256, 8), 256, 0, w->A, w->n_slices, part,
+                   w->needmask.p, 3);
+    }
     const int64_t n_send_items = (int64_t)world * (h.begin[me + 1] - h.begin[me]), n_recv_items = n;
     const int64_t n_items = std::max(n_send_items, n_recv_items);
     w->tmp_i32b.reserve((size_t)n_items + 1);       // flags
@@ -1383,6 +1405,7 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     DevBuf<float> &co_Af = local ? w->co_Af2 : w->co_Af;
     const int64_t row_lo = local ? w->row_begin : 0, row_hi = local ? w->row_end : n;
     const int world = local ? std::max(1, w->halo.world) : 1;
+    const int world_all = std::max(1, w->halo.world);
     if (local) w->nc2 = 0;
     else { w->two_level = false; w->nc = 0; }
     // every exit that leaves the level unbuilt says why (pdn_info / the bench line / the caller's error text)
@@ -1402,9 +1425,12 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     const int64_t raw_target = (int64_t)target * world;
 
     // bounding box of the vertices
-    const int bgrid = pdn_grid(ctx, ctx->geo_n_v, CO_BLK, 4);
+    // (partitioned assembly: only this rank's vertices are sure to be resident -- box of those, then the union over the ranks)
+    const int64_t bv0 = w->part ? std::min<int64_t>(w->row_begin, ctx->geo_n_v) : 0;
+    const int64_t bv1 = w->part ? std::min<int64_t>(w->row_end, ctx->geo_n_v) : ctx->geo_n_v;
+    const int bgrid = pdn_grid(ctx, std::max<int64_t>(bv1 - bv0, 1), CO_BLK, 4);
     w->co_tmp.reserve((size_t)4 * bgrid + 2048);
-    PDN_LAUNCH(ctx, bbox_kernel, bgrid, CO_BLK, 0, ctx->geo_n_v, (const double2 *)ctx->geo_xy, w->co_tmp.p);
+    PDN_LAUNCH(ctx, bbox_kernel, bgrid, CO_BLK, 0, bv1 - bv0, (const double2 *)ctx->geo_xy + bv0, w->co_tmp.p);
     std::vector<double> hb((size_t)4 * bgrid);
     PDN_CUDA(cudaMemcpyAsync(hb.data(), w->co_tmp.p, hb.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
     PDN_CUDA(cudaStreamSynchronize(st));
@@ -1412,6 +1438,17 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     for (int b = 0; b < bgrid; b++) {
         x0 = std::min(x0, hb[4 * b]); y0 = std::min(y0, hb[4 * b + 1]);
         x1 = std::max(x1, hb[4 * b + 2]); y1 = std::max(y1, hb[4 * b + 3]);
+    }
+    double n_entries_d = (double)n_entries;
+    if (w->part) {
+        double box[5] = {-x0, -y0, x1, y1, (double)n_entries};
+        w->tmp_f64a.reserve(8);
+        PDN_CUDA(cudaMemcpyAsync(w->tmp_f64a.p, box, sizeof box, cudaMemcpyHostToDevice, st));
+        pdn_comm_allreduce_max(ctx, w->tmp_f64a.p, 5);
+        PDN_CUDA(cudaMemcpyAsync(box, w->tmp_f64a.p, sizeof box, cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        x0 = -box[0]; y0 = -box[1]; x1 = box[2]; y1 = box[3];
+        n_entries_d = box[4] * world_all;       // bound on the stored entries of the whole operator (same on every rank)
     }
     if (!(x1 >= x0) || !(y1 >= y0)) return fail("degenerate bounding box");
 
@@ -1443,8 +1480,17 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         w->co_used.reserve((size_t)n_raw + 1);
         w->co_cid.reserve((size_t)n_raw + 1);
         PDN_CUDA(cudaMemsetAsync(w->co_used.p, 0, ((size_t)n_raw + 1) * sizeof(int32_t), st));
-        PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, row_lo, row_hi, g, ctx->geo_voff.p,
-                   (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, agg.p, w->co_used.p);
+        if (w->part && !local) {
+            // every rank bins its own rows (their coordinates are resident), the raw ids are all-gathered, and the
+            // occupancy of the bins is read off the gathered array: identical compact ids everywhere
+            PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->row_begin, w->row_end, g,
+                       ctx->geo_voff.p, (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, agg.p, w->co_used.p);
+            pdn_comm_allgatherv_i32(ctx, agg.p, w->halo.begin.data());
+            PDN_LAUNCH(ctx, agg_used_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, agg.p, w->co_used.p);
+        } else {
+            PDN_LAUNCH(ctx, agg_raw_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, row_lo, row_hi, g, ctx->geo_voff.p,
+                       (const double2 *)ctx->geo_xy, w->perm.p, w->map.p, agg.p, w->co_used.p);
+        }
         pdn_exclusive_scan_i32(ctx, w->co_used.p, n_raw, w->co_cid.p);
         PDN_CUDA(cudaMemcpyAsync(&nc, w->co_cid.p + n_raw, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         PDN_CUDA(cudaStreamSynchronize(st));
@@ -1455,17 +1501,11 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     }
     PDN_LAUNCH(ctx, agg_final_kernel, pdn_grid(ctx, n, CO_BLK, 8), CO_BLK, 0, n, w->co_cid.p, agg.p);
 
-    // fixed-point scale of A_c: |sum| <= entries * largest diagonal must stay below 2^62
-    const int mgrid = pdn_grid(ctx, n, CO_BLK, 4);
-    PDN_LAUNCH(ctx, min_kernel, mgrid, CO_BLK, 0, n, w->dinv.p, w->co_tmp.p);
-    std::vector<double> hm((size_t)mgrid);
-    PDN_CUDA(cudaMemcpyAsync(hm.data(), w->co_tmp.p, hm.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
-    PDN_CUDA(cudaStreamSynchronize(st));
-    double dmin = 1e300;
-    for (double v : hm) dmin = std::min(dmin, v);
-    if (!(dmin > 0.0) || !(dmin < 1e300)) return fail("non-positive Jacobi diagonal");
-    const double amax = 1.0 / dmin;
-    const double fix = exp2(floor(log2(4.0e18 / ((double)std::max<int64_t>(n_entries, 1) * amax))));
+    // fixed-point scale of A_c: |sum| <= entries * largest diagonal must stay below 2^62 (amax: the solve's, the
+    // same on every rank)
+    const double amax = w->amax;
+    if (!(amax > 0.0) || !(amax < 1e300)) return fail("non-positive Jacobi diagonal");
+    const double fix = exp2(floor(log2(4.0e18 / (std::max(n_entries_d, 1.0) * amax))));
 
     const size_t nc2 = (size_t)nc * nc;
     w->co_acc.reserve(nc2);
@@ -1473,6 +1513,9 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     PDN_CUDA(cudaMemsetAsync(w->co_acc.p, 0, nc2 * sizeof(long long), st));
     PDN_LAUNCH(ctx, coarse_accum_kernel, pdn_grid(ctx, w->n_slices * 32, CO_BLK, 8), CO_BLK, 0, w->A, w->n_slices, agg.p,
                nc, fix, (unsigned long long *)w->co_acc.p);
+    // partitioned: the SELL part above held this rank's rows only -- exact integer sum over the ranks; the override
+    // rows (every rank holds them all) are added afterwards, once
+    if (w->part && !local) pdn_comm_allreduce_sum_i64(ctx, w->co_acc.p, (int)nc2);
     if (w->A.n_special > 0)
         PDN_LAUNCH(ctx, coarse_accum_special_kernel, pdn_blocks(w->A.n_special, CO_BLK), CO_BLK, 0, w->A, agg.p, nc, fix,
                    (unsigned long long *)w->co_acc.p);
@@ -1722,7 +1765,26 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     if (nT > 0) PDN_LAUNCH(ctx, flag_u8_kernel, pdn_blocks(nT, 256), 256, 0, nT, w->sp_row_old.p, w->special.p);
     PDN_LAUNCH(ctx, sell_len_kernel, pdn_grid(ctx, n_pad, 256, 8), 256, 0, n, n_pad, L.indptr.p, L.indices.p, w->map.p,
                w->special.p, w->len.p);
-    PDN_LAUNCH(ctx, sell_sort_kernel, (int)(n_pad / SELL_WIN), SELL_WIN, 0, w->len.p, w->perm.p, w->inv.p);
+    // partitioned setup: the row ranges of the ranks (whole sort windows), known before the operator exists
+    const int world = pdn_comm_world(ctx), me = pdn_comm_rank(ctx);
+    std::vector<int64_t> part_begin(world + 1, 0);
+    pdn_row_partition(n, world, part_begin.data());
+    w->part = world > 1 && ctx->part_valid;
+    if (w->part && (ctx->part_n_nodes != n || ctx->part_lo != part_begin[me] || ctx->part_hi != part_begin[me + 1]))
+        PDN_FAIL(PDN_EINVAL, "solve: the system was assembled for another partition (n_nodes %lld, rows %lld..%lld)",
+                 (long long)ctx->part_n_nodes, (long long)ctx->part_lo, (long long)ctx->part_hi);
+    if (world > 1 && !w->part && ctx->part_valid) PDN_FAIL(PDN_EINVAL, "solve: partitioned system without a communicator");
+    const int64_t own_win0 = w->part ? part_begin[me] / SELL_WIN : 0;
+    const int64_t own_win1 = w->part ? (me == world - 1 ? n_pad / SELL_WIN : part_begin[me + 1] / SELL_WIN) : n_pad / SELL_WIN;
+    if (own_win1 > own_win0)
+        PDN_LAUNCH(ctx, sell_sort_kernel, (int)(own_win1 - own_win0), SELL_WIN, 0, w->len.p, w->perm.p, w->inv.p, own_win0);
+    if (w->part) {
+        // every rank sorted its own windows (it alone knows its rows' lengths): all-gather the permutation
+        std::vector<int64_t> bp(part_begin);
+        bp[world] = n_pad;
+        pdn_comm_allgatherv_i32(ctx, w->perm.p, bp.data());
+        pdn_comm_allgatherv_i32(ctx, w->inv.p, bp.data());
+    }
     PDN_LAUNCH(ctx, sell_width_kernel, pdn_grid(ctx, n_slices, 256, 8), 256, 0, n_slices, w->len.p, w->perm.p, w->scnt.p);
     pdn_exclusive_scan_i32(ctx, w->scnt.p, n_slices, w->soff.p);
     int32_t sell_total = 0;
@@ -1731,9 +1793,17 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     if (sell_total < 0) PDN_FAIL(PDN_EUNSUPPORTED, "solve: padded operator exceeds int32 indexing");
     w->s_ci.reserve((size_t)sell_total + 64);
     w->s_va.reserve((size_t)sell_total + 64);
-    PDN_LAUNCH(ctx, sell_fill_kernel, pdn_grid(ctx, n_slices * 32, 256, 8), 256, 0, n, n_slices, L.indptr.p, L.indices.p,
-               L.data.p, w->map.p, w->special.p, w->perm.p, w->inv.p, w->soff.p, w->s_ci.p, w->s_va.p, w->smask.p,
-               w->dinv.p);
+    {
+        const int64_t fs0 = own_win0 * (SELL_WIN / SELL_C), fs1 = own_win1 * (SELL_WIN / SELL_C);
+        if (w->part) {     // the slices of other ranks: no override mask, unit diagonal
+            PDN_CUDA(cudaMemsetAsync(w->smask.p, 0, (size_t)n_slices * sizeof(uint32_t), st));
+            PDN_LAUNCH(ctx, ones_kernel, pdn_grid(ctx, n_pad, BLK, 8), BLK, 0, n_pad, w->dinv.p);
+        }
+        if (fs1 > fs0)
+            PDN_LAUNCH(ctx, sell_fill_kernel, pdn_grid(ctx, (fs1 - fs0) * 32, 256, 8), 256, 0, n, fs1, L.indptr.p, L.indices.p,
+                       L.data.p, w->map.p, w->special.p, w->perm.p, w->inv.p, w->soff.p, w->s_ci.p, w->s_va.p, w->smask.p,
+                       w->dinv.p, fs0);
+    }
 
     trace.mark("sell");
     // g = r_n - L_nn o
@@ -1845,6 +1915,13 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         double dmin = 1e300;
         for (double v : h_dmin) dmin = std::min(dmin, v);
         w->amax = dmin > 0.0 && dmin < 1e300 ? 1.0 / dmin : 0.0;
+        if (w->part) {     // every rank saw its own rows' diagonals only
+            w->tmp_f64a.reserve(4);
+            PDN_CUDA(cudaMemcpyAsync(w->tmp_f64a.p, &w->amax, sizeof(double), cudaMemcpyHostToDevice, st));
+            pdn_comm_allreduce_max(ctx, w->tmp_f64a.p, 1);
+            PDN_CUDA(cudaMemcpyAsync(&w->amax, w->tmp_f64a.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+            PDN_CUDA(cudaStreamSynchronize(st));
+        }
     }
     w->n_special = nT;
     w->A.n = n;
@@ -1966,6 +2043,7 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
         const bool can_v2 = method == PDN_METHOD_PCG && w->two_level && (!is_dist(ctx) || pdn_peer_enabled(ctx));
         const bool want_v2 = e ? strcmp(e, "v2") == 0 : is_dist(ctx);
         w->v2 = can_v2 && want_v2;
+        w->halo_fused = w->v2 && halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0);
         if (w->v2) {
             w->tab.reserve((size_t)w->nc * TAB_STRIDE + 8);
             w->tab2.reserve((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8);
@@ -1978,6 +2056,13 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             PDN_CUDA(cudaMemsetAsync(w->rc2_d.p, 0, c2 * sizeof(double), st));
             PDN_CUDA(cudaMemsetAsync(w->cs2_d.p, 0, c2 * sizeof(double), st));
             if (w->nc2 == 0) { w->rc_fix2.reserve(8); w->xc2.reserve(8); w->co_Af2.reserve(8); }
+            {   // the range of aggregates this rank's rows touch: what its c_w exchange carries
+                const int32_t init[2] = {0x7fffffff, -1};
+                w->agg_range.reserve(8);
+                PDN_CUDA(cudaMemcpyAsync(w->agg_range.p, init, sizeof init, cudaMemcpyHostToDevice, st));
+                PDN_LAUNCH(ctx, agg_range_kernel, pdn_grid(ctx, w->row_end - w->row_begin, 256, 4), 256, 0, w->row_begin, w->row_end,
+                           w->agg.p, w->agg_range.p);
+            }
             // restriction windows of the ring kernel's CTAs (same grid, same slice split)
             if (!w->xs) {
                 const int64_t slices = (w->row_end - w->row_begin + SELL_C - 1) / SELL_C;
@@ -2055,7 +2140,25 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     reset_scal(ctx, w, 0.0, 0.0, 0);
     launch_spmv<RESID>(ctx, full_operator(ctx, N), d_v, w->full_a.p, d_rhs, w);
     fetch_scal(ctx, w);
-    const double residual_norm = sqrt(w->h_sc->rr);
+    double residual_norm = sqrt(w->h_sc->rr);
+    if (w->part) {
+        // this rank's L holds its own node rows, the terminals and the extra rows: ||L v - r||^2 = the own node rows
+        // summed over the ranks + the extra rows (identical on every rank, counted once)
+        double parts[2] = {0.0, 0.0};
+        const int rgrid = pdn_grid(ctx, std::max<int64_t>(w->row_end - w->row_begin, 1), RPB, 8);
+        PDN_LAUNCH(ctx, sumsq_kernel<true>, rgrid, RPB, 0, w->row_begin, w->row_end, w->full_a.p, (const double *)nullptr,
+                   w->d_sc, w->d_out, w->partials.p);
+        dist_reduce<7>(ctx, w);
+        PDN_CUDA(cudaMemcpyAsync(&parts[0], w->d_out, sizeof(double), cudaMemcpyDeviceToHost, st));
+        PDN_CUDA(cudaStreamSynchronize(st));
+        if (N > n) {
+            PDN_LAUNCH(ctx, sumsq_kernel<false>, pdn_grid(ctx, N - n, RPB, 8), RPB, 0, n, N, w->full_a.p, (const double *)nullptr,
+                       w->d_sc, w->d_out, w->partials.p);
+            PDN_CUDA(cudaMemcpyAsync(&parts[1], w->d_out, sizeof(double), cudaMemcpyDeviceToHost, st));
+            PDN_CUDA(cudaStreamSynchronize(st));
+        }
+        residual_norm = sqrt(parts[0] + parts[1]);
+    }
     if (!on_device) PDN_CUDA(cudaMemcpyAsync(v_out, d_v, N * sizeof(double), cudaMemcpyDeviceToHost, st));
     PDN_CUDA(cudaEventRecord(ev_end, st));
     PDN_CUDA(cudaEventSynchronize(ev_end));

@@ -53,7 +53,7 @@ def test_laplace_operator_unit_square():
     assert (np.diag(D) < 0).all() and np.array_equal(D, D.T) and np.allclose(D.sum(axis=1), 0)
 
 
-@pytest.mark.parametrize("path", golden_system_files()[:2], ids=os.path.basename)
+@pytest.mark.parametrize("path", golden_system_files(), ids=os.path.basename)
 def test_assemble_flat_and_solve_system(path):
     fs, d = load_system(path)
     L, r = S.assemble_flat(fs)
@@ -61,12 +61,34 @@ def test_assemble_flat_and_solve_system(path):
     assert np.array_equal(L.indptr, d["indptr"]) and np.array_equal(L.indices, d["indices"])
     assert np.array_equal(L.data, d["data"]) and np.array_equal(r, d["r"])
     assert L.tocsc().shape == L.shape                                   # benchmarks.py:652-654
-    v, info = S.solve_system(L, r)                                       # resident fast path
-    assert np.max(np.abs(v - d["v"])) <= 1e-6 * np.max(np.abs(d["v"]))
-    assert info.residual_norm < 1e-6 and abs(info.ground_node_current - d["ground_node_current"]) < 1e-7
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")                                   # no SolverWarning of any kind
+        v, info = S.solve_system(L, r)                                   # resident fast path
+    assert np.max(np.abs(v[:fs.n_nodes] - d["v"][:fs.n_nodes])) <= 1e-6 * np.max(np.abs(d["v"][:fs.n_nodes]))
+    # SolverInfo parity (padne/solver.py:775-777): the reference's own pass bar for the residual
+    # (tests/test_solver.py:2083-2089) and its ground current to 1e-9 A; the reference stays silent on these
+    # boards (np.isclose(ground, 0), solver.py:880-888), so must this
+    assert info.residual_norm < 1e-9
+    assert abs(info.ground_node_current - d["ground_node_current"]) < 1e-9
+    assert np.isclose(info.ground_node_current, 0) == np.isclose(d["ground_node_current"], 0)
     # a plain scipy matrix (e.g. the reference's own lil_matrix) takes the upload path
     v2, info2 = S.solve_system(scipy.sparse.lil_matrix(L), r)
     assert np.max(np.abs(v2 - d["v"])) <= 1e-6 * np.max(np.abs(d["v"]))
+
+
+def test_resident_token_survives_other_assemblies():
+    # assemble_system, then laplace_operator on the same context, then solve_system(L, r) must not solve
+    # whatever is resident now -- the stale handle takes the upload path and still gives the right answer
+    fs, d = load_system(golden_system_files()[0])
+    L, r = S.assemble_flat(fs)
+    other = DuckMesh([(0, 0), (1, 0), (1, 1), (0, 1), (0.5, 0.5)], [(0, 1, 4), (1, 2, 4), (2, 3, 4), (3, 0, 4)])
+    assert S.laplace_operator(other).shape == (5, 5)                    # replaces the resident matrix
+    v, info = S.solve_system(L, r)
+    assert np.max(np.abs(v[:fs.n_nodes] - d["v"][:fs.n_nodes])) <= 1e-6 * np.max(np.abs(d["v"][:fs.n_nodes]))
+    L2, r2 = S.assemble_flat(fs)                                         # and a fresh handle is resident again
+    v2, _ = S.solve_system(L2, r2)
+    assert np.max(np.abs(v2[:fs.n_nodes] - d["v"][:fs.n_nodes])) <= 1e-6 * np.max(np.abs(d["v"][:fs.n_nodes]))
 
 
 def test_solve_system_singular_behaves_like_superlu():
