@@ -454,7 +454,9 @@ def test_large_sub_boards_against_spsolve(ctx, name, board):
     v_ref, res_ref, ig_ref = oracle.solve(indptr, indices, data, rhs)
     assert info.rel_residual <= RESIDUAL_RTOL
     assert voltage_error(v, v_ref, fs.n_nodes) <= VOLTAGE_RTOL
-    # at this size the reference's own residual is 1e-9 ... 1e-8 and its ground current 4e-8 ... 2e-7 (it would
-    # warn); the Krylov solve has to be at least as tight
-    assert info.residual_norm <= max(2.0 * res_ref, 1e-9)
-    assert abs(info.ground_node_current) <= max(2.0 * abs(ig_ref), 1e-8)
+    # at this size the reference's own residual is 1e-9 ... 1e-8 (~1.3x the evaluation floor u amax ||u||) and its
+    # ground current 4e-8 ... 2e-7 (it would warn); the Krylov loop aims at 4x the floor (pdn_opts.atol), so it
+    # has to land within 4x of SuperLU's residual and within its ground current
+    assert info.residual_norm <= max(4.0 * res_ref, 1e-9)
+    assert info.residual_norm <= 8.0 * info.floor_abs
+    assert abs(info.ground_node_current) <= max(4.0 * abs(ig_ref), 1e-8)
