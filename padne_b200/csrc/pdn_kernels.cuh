@@ -240,12 +240,17 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
                                                               const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc,
                                                               const PeerLink *Lp, unsigned int *ticket,
                                                               const int32_t *__restrict__ agg2, long long *rc_fix2, int32_t nc2) {
-    __shared__ long long tab[CO_MAX];
-    __shared__ long long tab2[LOCAL ? CO_MAX : 1];   // rank-local second level
+    // Restriction tables: the 26-bit fixed-point value of a row goes in as TWO 14-bit limbs with native 32-bit shared
+    // atomics (ATOMS.ADD), straight from every lane -- no warp collective.  (Round 1 grouped the lanes of a warp by
+    // aggregate with match.any + redux.sync and added 64-bit sums, which on sm_100a is a CAS loop,
+    // ATOMS.CAST.SPIN.64; a 32-row warp holds 3.5 distinct aggregates on these meshes, so the collectives ran 3-4
+    // passes: 12-15 us per launch against 5 us for the plain update.  The integer sums are the same, so is the solve.)
+    __shared__ int tab[2][CO_MAX];
+    __shared__ int tab2[2][LOCAL ? CO_MAX : 1];   // rank-local second level
     pdl_trigger();
-    for (int a = threadIdx.x; a < nc; a += TLB) tab[a] = 0;
+    for (int a = threadIdx.x; a < nc; a += TLB) tab[0][a] = tab[1][a] = 0;
     if (LOCAL)
-        for (int a = threadIdx.x; a < nc2; a += TLB) tab2[a] = 0;
+        for (int a = threadIdx.x; a < nc2; a += TLB) tab2[0][a] = tab2[1][a] = 0;
     pdl_wait();
     if (sc->done) return;
     if (Lp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) peer_log(*Lp, 6);
@@ -256,7 +261,6 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
     const int64_t npair = (n - r0 + 1) >> 1;
     const int64_t per = ((npair + gridDim.x - 1) / gridDim.x + 31) & ~(int64_t)31;   // whole warps
     const int64_t t_lo = (int64_t)blockIdx.x * per, t_hi = t_lo + per < npair ? t_lo + per : npair;
-    const int lane = threadIdx.x & 31;
     __syncthreads();    // table cleared
     for (int64_t t0 = t_lo; t0 < t_hi; t0 += TLB) {
         const int64_t t = t0 + threadIdx.x;
@@ -288,21 +292,14 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
             r[i] = ra;
             a0 = agg[i];
         }
-        // warp-level sums per aggregate, then one shared-memory add per (warp, aggregate)
-        int q0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
-        int q1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
-        if (a1 == a0) { q0 += q1; a1 = -1; }
+        const int q0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
+        const int q1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
         {
-            const unsigned peers = __match_any_sync(0xffffffffu, a0);
-            const int sum = __reduce_add_sync(peers, q0);
-            if (lane == __ffs(peers) - 1 && a0 >= 0 && sum != 0)
-                atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a0]), (unsigned long long)(long long)sum);
-        }
-        if (__any_sync(0xffffffffu, a1 >= 0)) {
-            const unsigned peers = __match_any_sync(0xffffffffu, a1);
-            const int sum = __reduce_add_sync(peers, q1);
-            if (lane == __ffs(peers) - 1 && a1 >= 0 && sum != 0)
-                atomicAdd(reinterpret_cast<unsigned long long *>(&tab[a1]), (unsigned long long)(long long)sum);
+            int u0 = q0, u1 = q1;
+            int32_t b1 = a1;
+            if (b1 == a0) { u0 += u1; b1 = -1; }
+            if (a0 >= 0 && u0 != 0) { atomicAdd(&tab[0][a0], u0 & 0x3fff); atomicAdd(&tab[1][a0], u0 >> 14); }
+            if (b1 >= 0 && u1 != 0) { atomicAdd(&tab[0][b1], u1 & 0x3fff); atomicAdd(&tab[1][b1], u1 >> 14); }
         }
         if (LOCAL) {   // the same entries into the rank-local level's table
             int32_t b0 = -1, b1 = -1;
@@ -313,30 +310,19 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
             } else if (act) {
                 b0 = agg2[i];
             }
-            int p0 = max(min(__double2int_rn(ra * fix), 33554431), -33554431);
-            int p1 = max(min(__double2int_rn(rb * fix), 33554431), -33554431);
-            if (b1 == b0) { p0 += p1; b1 = -1; }
-            {
-                const unsigned peers = __match_any_sync(0xffffffffu, b0);
-                const int sum = __reduce_add_sync(peers, p0);
-                if (lane == __ffs(peers) - 1 && b0 >= 0 && sum != 0)
-                    atomicAdd(reinterpret_cast<unsigned long long *>(&tab2[b0]), (unsigned long long)(long long)sum);
-            }
-            if (__any_sync(0xffffffffu, b1 >= 0)) {
-                const unsigned peers = __match_any_sync(0xffffffffu, b1);
-                const int sum = __reduce_add_sync(peers, p1);
-                if (lane == __ffs(peers) - 1 && b1 >= 0 && sum != 0)
-                    atomicAdd(reinterpret_cast<unsigned long long *>(&tab2[b1]), (unsigned long long)(long long)sum);
-            }
+            int u0 = q0, u1 = q1;
+            if (b1 == b0) { u0 += u1; b1 = -1; }
+            if (b0 >= 0 && u0 != 0) { atomicAdd(&tab2[0][b0], u0 & 0x3fff); atomicAdd(&tab2[1][b0], u0 >> 14); }
+            if (b1 >= 0 && u1 != 0) { atomicAdd(&tab2[0][b1], u1 & 0x3fff); atomicAdd(&tab2[1][b1], u1 >> 14); }
         }
     }
     __syncthreads();
     for (int a = threadIdx.x; a < nc; a += TLB) {
-        const long long v = tab[a];
+        const long long v = ((long long)tab[1][a] << 14) + (long long)tab[0][a];
         if (v != 0) atomicAdd(&rc[a], (unsigned long long)v);
     }
     for (int a = threadIdx.x; LOCAL && a < nc2; a += TLB) {
-        const long long v = tab2[a];
+        const long long v = ((long long)tab2[1][a] << 14) + (long long)tab2[0][a];
         if (v != 0) atomicAdd(&rc2[a], (unsigned long long)v);
     }
     if (Lp == nullptr) return;
