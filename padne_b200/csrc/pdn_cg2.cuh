@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(SX_BLK, 2) sell_xs_kernel(SellOp A, XsPlan P, 
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }
-    if (MODE == CG2 && DIST && Lp != nullptr && cg.halo != nullptr) {     // the peers' interface entries of x
+    if (DIST && Lp != nullptr && cg.halo != nullptr) {     // the peers' interface entries of x (consumer-side wait)
         peer_halo_wait(*Lp, *cg.halo);
         __syncthreads();
     }

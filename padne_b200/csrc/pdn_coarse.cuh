@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
                 if (g[u] >= 0) dst[g[u]] = v[u];
         }
     }
-    peer_halo_tail(L, hs);
+    peer_halo_post(L, hs);      // the reader waits (peer_halo_wait at the start of the SpMV, pdn_peer_prim.cuh)
 }
 
 // restriction of one residual entry into the fixed-point accumulator (called by the update kernels,

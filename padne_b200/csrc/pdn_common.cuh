@@ -260,9 +260,9 @@ constexpr size_t PDN_PA_HALO_FLAG = 0;                              // [PEER_MAX
 constexpr size_t PDN_PA_RED_FLAG = 16;                              // [2][PEER_MAX]
 constexpr size_t PDN_PA_RC_FLAG = 32;                               // [2][PEER_MAX]
 constexpr size_t PDN_PA_CW_FLAG = 48;                               // [2][PEER_MAX] merged dots + c_w exchange (pdn_cg2.cuh)
-constexpr size_t PDN_PA_RED_VAL = 64;                               // [2][PEER_MAX][4]
-constexpr size_t PDN_PA_RC_SLOT = 2 * PDN_CO_MAX;                   // both parities of the fixed-point r_c
-constexpr size_t PDN_PA_RC_VAL = 128;                               // [2][PEER_MAX][RC_SLOT]
+constexpr size_t PDN_PA_RED_VAL = 64;                               // [2][PEER_MAX][8] flag-in-word pairs of 3 doubles
+constexpr size_t PDN_PA_RC_SLOT = 2 * PDN_CO_MAX + 8;               // header + two flag-in-word words per 64-bit entry
+constexpr size_t PDN_PA_RC_VAL = 192;                               // [2][PEER_MAX][RC_SLOT]
 constexpr size_t PDN_PA_CW_VAL = PDN_PA_RC_VAL + (size_t)2 * PDN_PEER_MAX * PDN_PA_RC_SLOT;   // [2][PEER_MAX][RC_SLOT]: 4 header words + c_w
 constexpr size_t PDN_PA_VEC = PDN_PA_CW_VAL + (size_t)2 * PDN_PEER_MAX * PDN_PA_RC_SLOT;   // [4][n_cap]
 constexpr int PDN_PA_NVEC = 4;            // halo-exchanged vectors living in the arena: z, ph, sh, x

@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
                                                               double *__restrict__ x, double *__restrict__ r,
                                                               const int32_t *__restrict__ agg, long long *rc_fix, int32_t nc,
                                                               const PeerLink *Lp, unsigned int *ticket,
-                                                              const int32_t *__restrict__ agg2, long long *rc_fix2, int32_t nc2) {
+                                                              const int32_t *__restrict__ agg2, long long *rc_fix2, int32_t nc2,
+                                                              const int32_t *arange) {
     // Restriction tables: the 26-bit fixed-point value of a row goes in as TWO 14-bit limbs with native 32-bit shared
     // atomics (ATOMS.ADD), straight from every lane -- no warp collective.  (Round 1 grouped the lanes of a warp by
     // aggregate with match.any + redux.sync and added 64-bit sums, which on sm_100a is a CAS loop,
@@ -335,7 +336,7 @@ __global__ void __launch_bounds__(TLB, 1) cg_update_tl_kernel(int64_t r0, int64_
     if (!is_last) return;
     if (threadIdx.x == 0) *ticket = 0u;
     __threadfence();
-    peer_sum_i64_cta(*Lp, reinterpret_cast<long long *>(rc), nc);
+    peer_sum_i64_cta(*Lp, reinterpret_cast<long long *>(rc), nc, arange);
 }
 
 // start / restart from the residual r:  z = dinv r (or its restriction, TL);  p = s = 0

@@ -57,25 +57,9 @@ __global__ void halo_wait_kernel(PeerLink L, HaloSend h) {
 // WHICH as in scalar_kernel.
 template <int WHICH>
 __global__ void peer_reduce_kernel(PeerLink L, Scal *sc, double *out) {
-    const int k = threadIdx.x;   // one warp
-    const unsigned long long e = L.epoch[1] + 1;
-    const size_t slot = (size_t)(e & 1) * PEER_MAX;
-    if (k < L.world) {
-        double *dst = reinterpret_cast<double *>(L.arena[k] + PA_RED_VAL) + (slot + L.me) * 4;
-        dst[0] = sc->part[0]; dst[1] = sc->part[1]; dst[2] = sc->part[2];
-        __threadfence_system();
-        st_release_sys(L.arena[k] + PA_RED_FLAG + slot + L.me, e);
-    }
-    bool ok = true;
-    if (k < L.world) ok = peer_wait(L.arena[L.me] + PA_RED_FLAG + slot + k, e, L.status, L.epoch + 5);
-    ok = __all_sync(0xffffffffu, ok);
-    if (k != 0) return;
-    L.epoch[1] = e;
-    double acc[3] = {0.0, 0.0, 0.0};
-    const volatile double *src = reinterpret_cast<const volatile double *>(L.arena[L.me] + PA_RED_VAL) + slot * 4;
-    for (int r = 0; r < L.world; r++) {
-        acc[0] += src[r * 4 + 0]; acc[1] += src[r * 4 + 1]; acc[2] += src[r * 4 + 2];
-    }
+    double acc[3] = {sc->part[0], sc->part[1], sc->part[2]};      // one warp; lane 0's copy is the one that counts
+    const bool ok = peer_allreduce3(L, acc);
+    if (threadIdx.x != 0) return;
     if (!ok) { sc->done = 3; sc->breakdown = 1; return; }
     sc->part[0] = acc[0]; sc->part[1] = acc[1]; sc->part[2] = acc[2];
     if (WHICH != RESID && WHICH != 7 && WHICH != 6 && sc->done) return;
@@ -89,30 +73,8 @@ __global__ void peer_reduce_kernel(PeerLink L, Scal *sc, double *out) {
 // the active slot of rc_fix (this rank's fixed-point partial sums, nc values; slot < 0: iteration parity)
 // -> exact sum over the ranks, in place
 __global__ void __launch_bounds__(256) peer_sum_i64_kernel(PeerLink L, const Scal *__restrict__ sc, long long *rc_fix, int32_t nc,
-                                                           int rc_slot) {
+                                                           int rc_slot, const int32_t *arange) {
     if (sc->done) return;    // identical on every rank
     long long *rc = rc_fix + (size_t)(rc_slot < 0 ? (sc->iter & 1) : rc_slot) * nc;
-    const int32_t cnt = nc;
-    const unsigned long long e = L.epoch[2] + 1;
-    const size_t slot = (size_t)(e & 1) * PEER_MAX;
-    for (int k = 0; k < L.world; k++) {
-        long long *dst = reinterpret_cast<long long *>(L.arena[k] + PA_RC_VAL) + (slot + L.me) * PA_RC_SLOT;
-        for (int j = threadIdx.x; j < cnt; j += 256) dst[j] = rc[j];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x < L.world) st_release_sys(L.arena[threadIdx.x] + PA_RC_FLAG + slot + L.me, e);
-    __shared__ int ok;
-    if (threadIdx.x == 0) ok = 1;
-    __syncthreads();
-    if (threadIdx.x < L.world && !peer_wait(L.arena[L.me] + PA_RC_FLAG + slot + threadIdx.x, e, L.status, L.epoch + 6)) ok = 0;
-    __syncthreads();
-    if (threadIdx.x == 0) L.epoch[2] = e;
-    if (!ok) return;
-    const volatile long long *src = reinterpret_cast<const volatile long long *>(L.arena[L.me] + PA_RC_VAL) + slot * PA_RC_SLOT;
-    for (int j = threadIdx.x; j < cnt; j += 256) {
-        long long s = 0;
-        for (int r = 0; r < L.world; r++) s += src[(size_t)r * PA_RC_SLOT + j];
-        rc[j] = s;
-    }
+    peer_sum_i64_cta(L, rc, nc, arange);
 }

@@ -297,11 +297,11 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
     if (MODE != PLAIN && MODE != RESID) {
         if (sc->done) return;
     }
-    if (MODE == CG2) {
-        // several GPUs, halo fused into K3: wait here for the peers' interface entries of x (consumer-side wait)
-        if (DIST && Lp != nullptr && cg.halo != nullptr) peer_halo_wait(*Lp, *cg.halo);
-        __syncthreads();      // restriction windows cleared, halo entries in place
-    }
+    // several GPUs, halo pushed by the tail of the kernel that wrote x (coarse_z_kernel / cg_update2_kernel): wait
+    // here for the peers' interface entries (consumer-side wait, pdn_peer_prim.cuh)
+    const bool halo_wait = DIST && Lp != nullptr && cg.halo != nullptr;
+    if (halo_wait) peer_halo_wait(*Lp, *cg.halo);
+    if (MODE == CG2 || halo_wait) __syncthreads();      // restriction windows cleared, halo entries in place
     const double fix = MODE == CG2 ? restrict_fix(sc) : 0.0;
 #if PDN_SELL_EVICT
     const uint64_t l2pol = tma::policy_evict_first();

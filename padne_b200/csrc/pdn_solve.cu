@@ -417,7 +417,10 @@ static void dist_reduce(pdn_ctx *ctx, SolveWork *w);
 // the scalar recurrence runs in scalar_kernel; x must already hold the halo entries.
 template <int MODE>
 static void launch_sell(pdn_ctx *ctx, SolveWork *w, const double *x, double *y, const double *aux) {
-    const Cg2 no_cg{};
+    Cg2 no_cg{};
+    // several GPUs: the vector's interface entries were pushed by the tail of the kernel that wrote it (or by the
+    // explicit exchange kernels, whose wait has then already happened): the SpMV waits for the peers' flags
+    no_cg.halo = w->halo_fused ? w->halo.peer_d.p : nullptr;
     if (is_dist(ctx)) {
         if (w->xs) launch_xs_kernel<MODE, true>(ctx, w, x, y, aux, no_cg);
         else launch_sell_kernel<MODE, true>(ctx, w, x, y, aux);
@@ -732,7 +735,8 @@ void enqueue_coarse_correction(pdn_ctx *ctx, SolveWork *w, int vgrid, int slot, 
     if (is_dist(ctx)) {
         if (!pdn_peer_enabled(ctx)) pdn_comm_allreduce_sum_i64(ctx, w->rc_fix.p, 2 * w->nc);
         else if (!rc_summed)
-            PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, slot);
+            PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, slot,
+                       (const int32_t *)w->agg_range.p);
     }
     const int cgrid = (w->nc + CO_RB - 1) / CO_RB;
     const int32_t nc2 = with_local ? w->nc2 : 0;
@@ -777,7 +781,7 @@ void enqueue_pcg_iteration(pdn_ctx *ctx, SolveWork *w, int vgrid) {
         const int tgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm * tl_per_sm, (npair + TLB - 1) / TLB));
         PDN_LAUNCH_PDL(ctx, w->pdl, kern, tgrid, TLB, 0, r0, r1, w->d_sc, w->w.p, w->z.p, w->p.p, w->s.p, w->x.p,
                        w->r.p, w->agg.p, w->rc_fix.p, w->nc, peer_link_or_none(ctx), &w->d_sc->ticket[3],
-                       w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p, w->nc2);
+                       w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p, w->nc2, (const int32_t *)w->agg_range.p);
         enqueue_coarse_correction(ctx, w, vgrid, -1, CO_BOOST32, w->r.p, w->z.p, /*rc_summed=*/pdn_peer_enabled(ctx),
                                   /*with_local=*/true);
     } else {
@@ -805,11 +809,22 @@ static void launch_update2(pdn_ctx *ctx, SolveWork *w, int vgrid) {
             if (w->z.p == pdn_peer_vec(ctx, v)) which = v;
         if (which < 0) PDN_FAIL(PDN_ECUDA, "update: z is not inside the peer arena");
         const int64_t npair = (r1 - r0 + 1) / 2;
-        const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));
-        PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<1024, ZONLY>), zgrid, 1024, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
-                       w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, pdn_peer_link_dev(ctx), w->halo.peer_d.p,
-                       pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx), w->tab.p, w->nc, w->tab2.p,
-                       w->nc2);
+        // 512 threads, two CTAs per SM: the body runs like the single-GPU kernel, and 296 tickets do not queue
+        // (PADNE_B200_K3=1024: one 1024-thread CTA per SM, the round-1 shape of this tail)
+        const char *e = getenv("PADNE_B200_K3");
+        if (e && strcmp(e, "1024") == 0) {
+            const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->n_sm, (npair + 1023) / 1024));
+            PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<1024, ZONLY>), zgrid, 1024, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
+                           w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, pdn_peer_link_dev(ctx), w->halo.peer_d.p,
+                           pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx), w->tab.p, w->nc, w->tab2.p,
+                           w->nc2);
+        } else {
+            const int zgrid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)2 * ctx->n_sm, (npair + 511) / 512));
+            PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<512, ZONLY>), zgrid, 512, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
+                           w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, pdn_peer_link_dev(ctx), w->halo.peer_d.p,
+                           pdn_peer_vec_offset(ctx, which), w->halo.send_idx.p, pdn_peer_ticket(ctx), w->tab.p, w->nc, w->tab2.p,
+                           w->nc2);
+        }
     } else {
         PDN_LAUNCH_PDL(ctx, w->pdl, (cg_update2_kernel<RPB, ZONLY>), vgrid, RPB, 0, r0, r1, w->d_sc, w->dinv.p, w->w.p, w->z.p,
                        w->p.p, w->s.p, w->x.p, w->r.p, w->agg.p, w->xc.p, agg2, xc2, (const PeerLink *)nullptr,
@@ -827,7 +842,8 @@ static void enqueue_pcg2_restrict(pdn_ctx *ctx, SolveWork *w, int vgrid) {
     PDN_LAUNCH(ctx, cg2_restrict_kernel<START>, vgrid, RPB, 0, r0, r1, w->d_sc, w->r.p, w->p.p, w->s.p, w->agg.p, w->rc_fix.p,
                w->nc2 > 0 ? w->agg2.p : (const int32_t *)nullptr, w->rc_fix2.p);
     if (is_dist(ctx))
-        PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, 0);
+        PDN_LAUNCH(ctx, peer_sum_i64_kernel, 1, 256, 0, pdn_peer_link(ctx), w->d_sc, w->rc_fix.p, w->nc, 0,
+                   (const int32_t *)w->agg_range.p);
     PDN_LAUNCH(ctx, cg2_convert_kernel<START>, std::max(1, (std::max(w->nc, w->nc2) + 255) / 256), 256, 0, w->d_sc, make_cg2(w),
                w->rc_fix.p, w->rc_fix2.p);
     w->pdl = saved_pdl;
@@ -2033,17 +2049,26 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             }
         }
     }
-    // Round-2 iteration (three kernels, ONE exchange of dots + coarse sums per iteration, pdn_cg2.cuh): the default
-    // on several GPUs with the peer-memory link, where an exchange costs 6-14 us (the NCCL fallback keeps the
-    // round-1 iteration).  On ONE GPU it measures slower than the round-1 iteration at 1M rows (54 against 47.5 us
-    // per iteration: the restriction + tail cost the SpMV 6 us, and the fused update moves the same ~100 B per row
-    // through L2 as the two kernels it replaces), so it is opt-in there.  PADNE_B200_PCG=v1 / v2 forces either.
+    // Round-2 iteration (three kernels, ONE exchange of dots + coarse sums per iteration, pdn_cg2.cuh): opt-in with
+    // PADNE_B200_PCG=v2.  Measured (round 2, B200): once the round-1 update kernel restricted with two-limb shared
+    // atomics instead of warp collectives, the four-kernel iteration is the faster one at every GPU count -- 43.4
+    // against 54 us per iteration on one GPU (1M DOF), 74.8 against 76.3 on two, 90.8 against 100.1 on four: the
+    // restriction + recurrence cost the SpMV 6 us, the fused update moves the same ~100 B per row through L2 as
+    // the two kernels it replaces, and the exchange saved (one of three) is worth 6-10 us.
     {
         const char *e = getenv("PADNE_B200_PCG");
         const bool can_v2 = method == PDN_METHOD_PCG && w->two_level && (!is_dist(ctx) || pdn_peer_enabled(ctx));
-        const bool want_v2 = e ? strcmp(e, "v2") == 0 : is_dist(ctx);
+        const bool want_v2 = e && strcmp(e, "v2") == 0;
         w->v2 = can_v2 && want_v2;
-        w->halo_fused = w->v2 && halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0);
+        if (is_dist(ctx) && w->two_level) {
+            // the range of aggregates this rank's rows touch: all its coarse-sum exchanges carry (both iterations)
+            const int32_t init[2] = {0x7fffffff, -1};
+            w->agg_range.reserve(8);
+            PDN_CUDA(cudaMemcpyAsync(w->agg_range.p, init, sizeof init, cudaMemcpyHostToDevice, st));
+            PDN_LAUNCH(ctx, agg_range_kernel, pdn_grid(ctx, std::max<int64_t>(w->row_end - w->row_begin, 1), 256, 4), 256, 0,
+                       w->row_begin, w->row_end, w->agg.p, w->agg_range.p);
+        }
+        w->halo_fused = halo_in_coarse_z(ctx, w) && (w->halo.n_send > 0 || w->halo.n_recv > 0);
         if (w->v2) {
             w->tab.reserve((size_t)w->nc * TAB_STRIDE + 8);
             w->tab2.reserve((size_t)std::max(w->nc2, 1) * TAB_STRIDE + 8);
@@ -2056,13 +2081,6 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
             PDN_CUDA(cudaMemsetAsync(w->rc2_d.p, 0, c2 * sizeof(double), st));
             PDN_CUDA(cudaMemsetAsync(w->cs2_d.p, 0, c2 * sizeof(double), st));
             if (w->nc2 == 0) { w->rc_fix2.reserve(8); w->xc2.reserve(8); w->co_Af2.reserve(8); }
-            {   // the range of aggregates this rank's rows touch: what its c_w exchange carries
-                const int32_t init[2] = {0x7fffffff, -1};
-                w->agg_range.reserve(8);
-                PDN_CUDA(cudaMemcpyAsync(w->agg_range.p, init, sizeof init, cudaMemcpyHostToDevice, st));
-                PDN_LAUNCH(ctx, agg_range_kernel, pdn_grid(ctx, w->row_end - w->row_begin, 256, 4), 256, 0, w->row_begin, w->row_end,
-                           w->agg.p, w->agg_range.p);
-            }
             // restriction windows of the ring kernel's CTAs (same grid, same slice split)
             if (!w->xs) {
                 const int64_t slices = (w->row_end - w->row_begin + SELL_C - 1) / SELL_C;
