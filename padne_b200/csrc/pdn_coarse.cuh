@@ -411,7 +411,7 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
             const double ca = aa.x >= 0 ? __ldg(&xc[aa.x]) : 0.0;
             double cb = aa.y == aa.x ? ca : (aa.y >= 0 ? __ldg(&xc[aa.y]) : 0.0);
             double ca2 = ca;
-            if (BLK == 1024 && agg2 != nullptr) {          // rank-local second level (multi-GPU instantiation only)
+            if (agg2 != nullptr) {          // rank-local second level (multi-GPU instantiation only)
                 const int2 bb = *reinterpret_cast<const int2 *>(agg2 + i);
                 const double la = bb.x >= 0 ? __ldg(&xc2[bb.x]) : 0.0;
                 ca2 += la;
@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(BLK) coarse_z_kernel(int64_t r0, int64_t n, co
         } else {
             const int32_t a = agg[i];
             double c = a >= 0 ? __ldg(&xc[a]) : 0.0;
-            if (BLK == 1024 && agg2 != nullptr) {
+            if (agg2 != nullptr) {
                 const int32_t b = agg2[i];
                 c += b >= 0 ? __ldg(&xc2[b]) : 0.0;
             }
