@@ -287,7 +287,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default=None, help="default: 2layer_1M at 1 GPU, stack_<2N>layer at N GPUs")
     ap.add_argument("--multi", default="partitioned", choices=["partitioned", "independent"])
-    ap.add_argument("--n", type=int, default=None, help="grid vertices per side (default: the config's full size)")
+    # (--grid: torchrun's own parser trips over "--n" after the script name -- ambiguous with --nnodes ...)
+    ap.add_argument("--n", "--grid", dest="n", type=int, default=None,
+                    help="grid vertices per side (default: the config's full size)")
     ap.add_argument("--impl", default="padne_b200", choices=["padne_b200", "reference"])
     ap.add_argument("--cpu-sample-n", type=int, default=260, help="grid size of the CPU-baseline sample (oracle port)")
     ap.add_argument("--ref-sample-n", type=int, default=160,

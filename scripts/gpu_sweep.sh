@@ -11,10 +11,10 @@ for n in 224 387 708 1225 2236 3873 5000; do
   [ "$N" -gt 1 ] && [ $n -gt 2236 ] && break          # per-GPU share of the stack stays under 10M DOF
   extra="--no-cpu-baseline"; [ $first = 1 ] && extra=""; first=0
   if [ "$N" = 1 ]; then
-    timeout 900 python bench.py --n $n --steps 3 --warmup 3 --no-named-configs $extra 2>gpurun_out/sweep_err.log | grep '^{' >> $out
+    timeout 900 python bench.py --grid $n --steps 3 --warmup 3 --no-named-configs $extra 2>gpurun_out/sweep_err.log | grep '^{' >> $out
   else
     timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 \
-      bench.py --gpus $N --n $n --steps 3 --warmup 3 --no-named-configs $extra 2>gpurun_out/sweep_err.log | grep '^{' >> $out
+      bench.py --gpus $N --grid $n --steps 3 --warmup 3 --no-named-configs $extra 2>gpurun_out/sweep_err.log | grep '^{' >> $out
   fi
   echo "n=$n exit ${PIPESTATUS[0]}"
 done
