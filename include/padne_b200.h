@@ -181,6 +181,26 @@ int pdn_spmv(pdn_ctx *ctx, const double *x, double *y, int on_device);
  * solver iteration and only the SpMV is bracketed by the events. */
 int pdn_bench_spmv(pdn_ctx *ctx, int32_t reps, int flush_l2, double *ms_per_launch);
 
+/* ---- r = b - A x and ||r||_2^2 WITHOUT any device allocation -----------------------------------------
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * A variant of the residual form of the CSR SpMV (the kernel behind pdn_spmv and pdn_info.residual_norm)
+ * whose reduction scratch is a fixed file-scope device array instead of context-owned cudaMalloc'd memory:
+ * the call makes no cudaMalloc / cudaFree / allocating library call and needs no pdn_ctx.
+ *   device: CUDA ordinal; stream: a cudaStream_t of that device cast to an integer (0 = default stream);
+ *   indptr [N+1], indices / data [nnz], x, b, r [N], rr [1]: DEVICE pointers, caller-owned;
+ *   r[i] = b[i] - sum_k data[k] * x[indices[k]] (stored order, every operation rounded separately: the
+ *   same bits as b - pdn_spmv(x)), rr[0] = sum_i r[i]^2 (fixed summation order: reproducible);
+ *   err (may be NULL) receives a message of up to err_cap bytes when the status is not PDN_OK.
+ * ASYNCHRONOUS: the work is queued on `stream`; r and rr are valid once the stream reaches that point.
+ * Limit: N <= PDN_NOALLOC_MAX_ROWS, larger N -> PDN_EUNSUPPORTED.  The scratch (131 328 bytes: one partial
+ * sum per 1024 rows) is held by every GPU that loads the library until the process exits, and is SHARED by
+ * all calls on a GPU: calls that overlap on one GPU (different streams or threads) race on it. */
+#define PDN_NOALLOC_MAX_ROWS 16777216 /* 2^24 */
+int pdn_residual_noalloc(int device, uint64_t stream, int64_t N, const int32_t *indptr, const int32_t *indices,
+                         const double *data, const double *x, const double *b, double *r, double *rr,
+                         char *err, int64_t err_cap);
+
 /* ---- multi-GPU: one process per GPU, NCCL over NVLink / NVSwitch -----------------------------------
  * No reference equivalent (the reference is single-threaded CPU code); this is the north star's
  * "large boards are partitioned across the GPUs of one box".  After pdn_comm_init every pdn_solve on

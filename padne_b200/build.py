@@ -26,6 +26,7 @@ UNITS = {
     "pdn_assemble.cu": ["-fmad=false"],
     "pdn_solve.cu": [],
     "pdn_multi.cu": [],
+    "pdn_noalloc.cu": [],       # self-contained: pdn_residual_noalloc and its file-scope device scratch
     "pdn_vtu.cpp": [],          # host only (row F4); nvcc hands it to g++
 }
 

@@ -26,7 +26,7 @@ METHOD_NAMES = {METHOD_PCG: "pcg", METHOD_BICGSTAB: "bicgstab"}
 # every symbol include/padne_b200.h declares (tests check that the library exports them all)
 SYMBOLS = ("pdn_create", "pdn_destroy", "pdn_strerror", "pdn_last_error", "pdn_launch_count",
            "pdn_stream", "pdn_element_weights", "pdn_assemble", "pdn_assemble_part", "pdn_get_csr", "pdn_get_shape",
-           "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_power_density",
+           "pdn_set_csr", "pdn_solve", "pdn_spmv", "pdn_bench_spmv", "pdn_residual_noalloc", "pdn_power_density",
            "pdn_comm_unique_id", "pdn_comm_init", "pdn_comm_destroy", "pdn_comm_info", "pdn_nearest_vertex",
            "pdn_format_f64", "pdn_vtu_piece_bound", "pdn_vtu_piece")
 
@@ -116,6 +116,7 @@ def load_library(path: str | None = None):
     lib.pdn_set_csr.argtypes = [P, I64, I64, P, P, P, ctypes.c_int]
     lib.pdn_solve.argtypes = [P, P, ctypes.POINTER(PdnOpts), P, ctypes.POINTER(PdnInfo), ctypes.c_int]
     lib.pdn_spmv.argtypes = [P, P, P, ctypes.c_int]
+    lib.pdn_residual_noalloc.argtypes = [ctypes.c_int, ctypes.c_uint64, I64, P, P, P, P, P, P, P, ctypes.c_char_p, I64]
     lib.pdn_bench_spmv.argtypes = [P, I32, ctypes.c_int, ctypes.POINTER(D)]
     lib.pdn_power_density.argtypes = [P, I64, P, P, I64, P, D, P, ctypes.c_int]
     lib.pdn_nearest_vertex.argtypes = [P, I32, P, P, P, I64, P, P, P, P, ctypes.c_int]
@@ -428,6 +429,28 @@ def vtu_piece(xy, tri, voltage) -> np.ndarray:
 _default_ctx: dict[int, Context] = {}
 
 
+NOALLOC_MAX_ROWS = 1 << 24
+
+
+def residual_noalloc(indptr, indices, data, x, b, r, rr, device: int = 0, stream: int = 0, n_rows: int | None = None) -> None:
+    """``pdn_residual_noalloc``: r = b - A x and rr[0] = ||r||^2 into CALLER-OWNED device tensors, with no device
+    allocation anywhere on the path (no reference counterpart; see include/padne_b200.h).  Asynchronous on
+    ``stream`` (a ``cudaStream_t`` as an integer; 0 = the default stream).  At most ``NOALLOC_MAX_ROWS`` rows."""
+    lib = load_library()
+    n = int(indptr.shape[0]) - 1 if n_rows is None else int(n_rows)
+    err = ctypes.create_string_buffer(512)
+    st = lib.pdn_residual_noalloc(int(device), int(stream), n, _ptr(indptr), _ptr(indices), _ptr(data), _ptr(x),
+                                  _ptr(b), _ptr(r), _ptr(rr), err, len(err))
+    if st == PDN_OK:
+        return
+    msg = err.value.decode() or f"pdn_residual_noalloc: {lib.pdn_strerror(st).decode()}"
+    if st == PDN_EINVAL:
+        raise ValueError(msg)
+    if st == PDN_EUNSUPPORTED:
+        raise NotImplementedError(msg)
+    raise RuntimeError(msg)
+
+
 def default_context(device: int = 0) -> Context:
     """Process-wide context per device (created on first use)."""
     ctx = _default_ctx.get(device)
@@ -438,4 +461,4 @@ def default_context(device: int = 0) -> Context:
 
 
 __all__ = ["Context", "default_context", "load_library", "SolveInfo", "SingularSystemError",
-           "NotConvergedError", "SYMBOLS", "LIB_PATH", "warnings"]
+           "NotConvergedError", "SYMBOLS", "LIB_PATH", "warnings", "residual_noalloc", "NOALLOC_MAX_ROWS"]
