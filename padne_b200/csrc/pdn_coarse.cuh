@@ -318,6 +318,271 @@ __global__ void __launch_bounds__(CO_BLK, 1) coarse_invert_kernel(int32_t nc, in
 }
 
 // ------------------------------------------------------------------------------------------------
+// Round-2 form of the same sweep (default; PADNE_B200_INVERT=v1 keeps the kernel above).  Measured with per-phase
+// cycle counters (-DPDN_INV_TIMING, nc = 1458, R = 16, 92 block steps), a step of the kernel above is a serial chain
+//   rank-16 update 24.2k cycles -> owner publishes its 16 rows 8.5k -> owner inverts D 7.1k -> c = A_iK D^-1 1.3k
+// = 41k cycles = 22 us, and the update itself runs at 1.2k cycles per row where the same loop in isolation
+// (scripts/micro/upd_loop.cu) needs 540: with 16 pivot rows x 3 columns of the published block in registers (96)
+// the loop sits on the 128-register ceiling and every broadcast LDS of c is issued only after the DFMAs of the
+// previous one (the form `acc += c.x * p + c.y * p'` also compiled to DMUL + DFMA + DADD).  Here:
+//   * RT = 12 rows per CTA (compile time): 72 registers of published rows, so the c loads run ahead of the DFMAs;
+//     per step the update is (12/16)^2 of the work, for 4/3 of the steps;
+//   * the update is a pure DFMA chain per entry, acc = fma(c_q, p_q, acc) starting from the entry itself;
+//   * the NEXT owner publishes its rows with one bulk copy shared -> global by the TMA engine as soon as its 15
+//     column warps are done (plain stores: 8.5k cycles as a separate copy, +6k when issued from the update loop);
+//   * warp 15 prepares the NEXT owner's D^-1: while the others update the rows, it forms the new diagonal block from
+//     the published rows with the same fma chain (same bits as the update will store), inverts it in shared memory
+//     with warp-level barriers only and publishes it; an owner therefore raises ONE flag, right after its fence, for
+//     rows and D^-1 together.  Warp 15 owns only the LAST 32 * NCOL columns of a pass (18 of 1458: one column per
+//     lane instead of three), so the inversion hides behind the other warps' update;
+//   * the others pull the published rows from L2 into registers before they form c = -A_iK D^-1.
+// Same sweep and pivot order as above; an entry differs in the last bit (fma chain instead of mul/fma/add).
+// ------------------------------------------------------------------------------------------------
+constexpr int INV_BLK = 512;               // columns per pass and per column-per-thread
+constexpr int INV_THREADS = 512;           // 16 warps (a 17th would be allocated as 20: 96 registers per thread)
+constexpr int INV_CW = INV_THREADS - 32;   // warps 0..14 own the first 480 * NCOL columns of a pass; warp 15, the
+                                           // inverter, the last 32 * NCOL (none at all when nc <= 480 * NCOL + ...)
+
+// In-place Gauss-Jordan of the n x n block in d (16 x 17 storage -- a 16-double row stride puts a whole column on one
+// pair of banks: 1000 cycles per pivot --, identity beyond n) by ONE warp:
+// lane = (row r = lane & 15, half h = lane >> 4) holds 8 entries.  Returns false on a non-positive pivot.
+__device__ __forceinline__ bool warp_invert_block(double (*d)[17], int n, int lane) {
+    const int r = lane & 15, h = lane >> 4;
+    bool ok = true;
+#pragma unroll 1
+    for (int q = 0; q < n; q++) {
+        __syncwarp();
+        const double p = d[q][q], cq = d[r][q];
+        double rq[8], cur[8];
+#pragma unroll
+        for (int c = 0; c < 8; c++) { rq[c] = d[q][8 * h + c]; cur[c] = d[r][8 * h + c]; }
+        __syncwarp();
+        ok = ok && (p > 0.0);
+        const double ip = 1.0 / p;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const int col = 8 * h + c;
+            const double pr = (col == q ? 1.0 : rq[c]) * ip;
+            d[r][col] = r == q ? pr : (col == q ? 0.0 : cur[c]) - cq * pr;
+        }
+    }
+    __syncwarp();
+    return ok;
+}
+
+__device__ __forceinline__ void inv_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void inv_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+// shared -> global bulk copy by the TMA engine (bytes: multiple of 16, both addresses 16 B aligned), and its completion
+__device__ __forceinline__ void inv_bulk_s2g(void *dst, const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(tma::smem_addr(src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void inv_bulk_commit_wait() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async;" ::: "memory");
+}
+__device__ __forceinline__ void inv_release(unsigned int *flag) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(flag), "r"(1u) : "memory");
+}
+
+template <int NCOL, int RT>
+__global__ void __launch_bounds__(INV_THREADS, 1) coarse_invert2_kernel(int32_t nc, double *__restrict__ A,
+                                                                        double *__restrict__ piv /*[n_blk + 1][RT * nc + 256]*/,
+                                                                        unsigned int *flags /*[2 * n_blk], zeroed*/,
+                                                                        int32_t *status, float *__restrict__ Af) {
+    extern __shared__ __align__(128) double rows[];  // [RT][nc]
+    __shared__ __align__(16) double cs[16][16];      // this step: D^-1 (owner) / -A_iK D^-1 (others); RT <= 16
+    __shared__ __align__(16) double cst[16][17];     // its transpose, for the inverter warp (conflict-free by row)
+    __shared__ __align__(16) double dv[16][16], ak[16][16];
+    __shared__ __align__(16) double dn[16][17];      // inverter warp: my diagonal block -> its inverse, one step ahead
+    __shared__ __align__(16) double pd[16][17];      // ... and the columns of that block in the published rows
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const bool inverter = tid >= INV_CW;             // warp 15
+    const int ir = lane & 15, ih = lane >> 4;        // inverter lane: row, half of the columns
+    const int r0 = b * RT;
+    const int nr = r0 >= nc ? 0 : (r0 + RT <= nc ? RT : nc - r0);
+    const int n_blk = (nc + RT - 1) / RT;
+    const size_t pstride = (size_t)RT * nc + 256;
+    for (int e = tid; e < nr * nc; e += INV_THREADS) {
+        const double v = A[(size_t)r0 * nc + e];
+        rows[e] = v;
+        if (b == 0) piv[e] = v;                      // the first owner's rows are published as they are
+    }
+    __syncthreads();
+    if (b == 0) {                                    // ... and its D^-1 has nobody to prepare it
+        if (inverter) {
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int col = 8 * ih + c;
+                dn[ir][col] = (ir < nr && col < nr) ? rows[ir * nc + col] : (ir == col ? 1.0 : 0.0);
+            }
+            if (!warp_invert_block(dn, nr, lane) && lane == 0) atomicExch(&status[0], PDN_ESINGULAR);
+#pragma unroll
+            for (int c = 0; c < 8; c++) piv[(size_t)RT * nc + ir * 16 + 8 * ih + c] = dn[ir][8 * ih + c];
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) { inv_release(flags + 0); inv_release(flags + 1); }
+    }
+    const int di = (tid >> 4) & 15, dj = tid & 15;   // threads 0..255: one per entry of a 16 x 16 block
+    const bool blk16 = tid < 256;
+#ifdef PDN_INV_TIMING
+    long long tw_b = 0, tw_a = 0, t_cs = 0, t_upd = 0, t_own_upd = 0, t_next_upd = 0, tc = clock64();
+    __shared__ long long t_invw[2];
+#define INV_TICK(acc) do { if (tid == 0) { const long long n_ = clock64(); acc += n_ - tc; tc = n_; } } while (0)
+#else
+#define INV_TICK(acc) do { } while (0)
+#endif
+    for (int kb = 0; kb < n_blk; kb++) {
+        const int k0 = kb * RT, nk = k0 + RT <= nc ? RT : nc - k0;
+        double *pb = piv + (size_t)kb * pstride;
+        double *pbn = piv + (size_t)(kb + 1) * pstride;      // publication slot of the next owner (used by it alone)
+        const bool owner = kb == b, next_owner = kb + 1 == b;
+        // flags[2 kb] = the owner's rows are in pb, flags[2 kb + 1] = its D^-1 is; both were raised during step kb - 1
+        if (owner) {
+            if (blk16) cs[di][dj] = dn[di][dj];      // (the step ended with a block-wide barrier: dn is complete)
+        } else {
+            if (!flag_wait(flags + 2 * kb, status)) return;
+            INV_TICK(tw_b);
+        }
+        // one pass per NCOL * INV_BLK columns (uniform trip count: the passes contain barriers)
+        for (int base = 0, pass = 0; base < nc; base += NCOL * INV_BLK, pass++) {
+            // columns of this thread in this pass
+            const int jbase = base + (inverter ? INV_CW * NCOL + lane : tid), jstep = inverter ? 32 : INV_CW;
+            double p[NCOL][RT];
+#pragma unroll
+            for (int t = 0; t < NCOL; t++) {
+                const int j = jbase + t * jstep;
+#pragma unroll
+                for (int q = 0; q < RT; q++)
+                    p[t][q] = (j < nc && q < nk) ? (owner ? rows[q * nc + j] : __ldcg(&pb[q * nc + j])) : 0.0;
+            }
+            if (pass == 0) {
+                if (!owner) {
+                    // the published rows are on their way into registers; now D^-1 and c = -A_iK D^-1
+                    if (!flag_wait(flags + 2 * kb + 1, status)) return;
+                    INV_TICK(tw_a);
+                    if (blk16) {
+                        dv[di][dj] = __ldcg(&pb[(size_t)RT * nc + tid]);
+                        ak[di][dj] = (di < nr && dj < nk) ? rows[di * nc + k0 + dj] : 0.0;
+                    }
+                    if (next_owner && inverter) {
+                        // my diagonal block BEFORE this step's update, and its columns of the published rows
+#pragma unroll
+                        for (int c = 0; c < 8; c++) {
+                            const int col = 8 * ih + c;
+                            dn[ir][col] = (ir < nr && col < nr) ? rows[ir * nc + r0 + col] : (ir == col ? 1.0 : 0.0);
+                            pd[ir][col] = (ir < nk && col < nr) ? __ldcg(&pb[ir * nc + r0 + col]) : 0.0;
+                        }
+                    }
+                    __syncthreads();
+                    if (blk16) {
+                        double c = 0.0;
+#pragma unroll
+                        for (int q = 0; q < 16; q++) c += ak[di][q] * dv[q][dj];
+                        cs[di][dj] = -c;
+                        cst[dj][di] = -c;
+                    }
+                }
+                __syncthreads();
+                INV_TICK(t_cs);
+            }
+            const int ni = owner ? nk : nr;
+            for (int i = 0; i < ni; i++) {
+                double acc[NCOL];
+#pragma unroll
+                for (int t = 0; t < NCOL; t++) {
+                    const int j = jbase + t * jstep;
+                    acc[t] = (owner || j >= nc) ? 0.0 : rows[i * nc + j];
+                }
+#pragma unroll
+                for (int q = 0; q < RT; q += 2) {
+                    const double2 c = *reinterpret_cast<const double2 *>(&cs[i][q]);
+#pragma unroll
+                    for (int t = 0; t < NCOL; t++) {
+                        acc[t] = fma(c.x, p[t][q], acc[t]);
+                        acc[t] = fma(c.y, p[t][q + 1], acc[t]);
+                    }
+                }
+#pragma unroll
+                for (int t = 0; t < NCOL; t++) {
+                    const int j = jbase + t * jstep;
+                    if (j >= nc) continue;
+                    rows[i * nc + j] = acc[t];               // (the pivot columns are overwritten below)
+                }
+            }
+        }
+        // Columns done.  In the next owner's CTA warp 15 only ARRIVES and goes on to its D^-1, the other 15 warps
+        // finish the rows and raise the rows flag without waiting for it; everywhere else this is a plain barrier.
+        if (next_owner && inverter) {
+            tma::fence_proxy_async();                // my columns of the rows, for the bulk copy below
+            inv_bar_arrive(1, INV_THREADS);
+#ifdef PDN_INV_TIMING
+            const long long ti0 = clock64();
+#endif
+            // this step's update of my diagonal block with the update's own fma chain (identical bits) ...
+            double val[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int col = 8 * ih + c;
+                double acc = dn[ir][col];
+#pragma unroll
+                for (int q = 0; q < RT; q += 2) {
+                    acc = fma(cst[q][ir], pd[q][col], acc);
+                    acc = fma(cst[q + 1][ir], pd[q + 1][col], acc);
+                }
+                val[c] = acc;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; c++) dn[ir][8 * ih + c] = val[c];
+            // ... and its inverse, published under its own flag
+            if (!warp_invert_block(dn, nr, lane) && lane == 0) atomicExch(&status[0], PDN_ESINGULAR);
+#pragma unroll
+            for (int c = 0; c < 8; c++) pbn[(size_t)RT * nc + ir * 16 + 8 * ih + c] = dn[ir][8 * ih + c];
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) inv_release(flags + 2 * (kb + 1) + 1);
+#ifdef PDN_INV_TIMING
+            if (lane == 0) t_invw[0] = clock64() - ti0;
+#endif
+        } else {
+            inv_bar_sync(1, INV_THREADS);
+            // the pivot columns of every row: D^-1 (owner) / -A_iK D^-1 (others), i.e. c itself
+            if (blk16 && di < (owner ? nk : nr) && dj < nk) rows[di * nc + k0 + dj] = cs[di][dj];
+            if (next_owner) {
+                // publish my rows: one bulk copy shared -> global by the TMA engine (the same stores issued from
+                // the update loop cost the next owner 6k cycles per step), then the rows flag
+                tma::fence_proxy_async();
+                inv_bar_sync(2, INV_CW);
+                if (tid == 0) {
+                    const uint32_t n_ent = (uint32_t)nr * (uint32_t)nc, n_even = n_ent & ~1u;
+                    for (uint32_t o = 0; o < n_even; o += 4096u)
+                        inv_bulk_s2g(pbn + o, rows + o, (n_even - o < 4096u ? n_even - o : 4096u) * 8u);
+                    if (n_ent & 1u) pbn[n_ent - 1] = rows[n_ent - 1];
+                    inv_bulk_commit_wait();
+                    __threadfence();
+                    inv_release(flags + 2 * (kb + 1));
+                }
+            }
+        }
+        __syncthreads();
+#ifdef PDN_INV_TIMING
+        if (owner) INV_TICK(t_own_upd); else if (next_owner) INV_TICK(t_next_upd); else INV_TICK(t_upd);
+#endif
+    }
+#ifdef PDN_INV_TIMING
+    if (tid == 0 && (b % 17 == 0 || b == n_blk - 1))
+        printf("[inv b=%d of %d] per other-step cycles: wait_rows %lld wait_dinv %lld cs %lld update %lld | as next owner: update+publish %lld (warp 15: block + inverse %lld) | as owner: update %lld\n",
+               b, n_blk, tw_b / (n_blk - 1), tw_a / (n_blk - 1), t_cs / (n_blk - 1), t_upd / (n_blk - 2), t_next_upd, t_invw[0], t_own_upd);
+#endif
+    for (int e = tid; e < nr * nc; e += INV_THREADS) {
+        A[(size_t)r0 * nc + e] = rows[e];
+        Af[(size_t)r0 * nc + e] = (float)rows[e];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // apply
 // ------------------------------------------------------------------------------------------------
 // x_c = A_c^-1 r_c  (r_c arrives in fixed point, in slot `slot`, or iteration & 1 if slot < 0, scaled by

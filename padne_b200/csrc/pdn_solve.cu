@@ -1538,24 +1538,47 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
     PDN_LAUNCH(ctx, coarse_convert_kernel, pdn_grid(ctx, (int64_t)nc2, CO_BLK, 8), CO_BLK, 0, nc, 1.0 / fix, w->co_acc.p,
                co_A.p, symmetric ? 1 : 0);
 
-    // inverse: cooperative blocked Gauss-Jordan, rows of the matrix resident in shared memory
-    // rows per CTA: the critical path is one R x R inverse + one rank-R update + one flag hand-over per
-    // block step, so blocks are as tall as shared memory allows
-    int32_t R = (int32_t)std::min<int64_t>(16, (int64_t)(200 * 1024) / ((int64_t)nc * 8));
-    if (const char *e = getenv("PADNE_B200_CO_R")) R = std::min<int32_t>(R, std::max(1, atoi(e)));   // tuning
-    R = std::max(R, (nc + ctx->n_sm - 1) / ctx->n_sm);
+    // inverse: cooperative blocked Gauss-Jordan, rows of the matrix resident in shared memory (pdn_coarse.cuh).
+    // Round-2 kernel: 12 rows per CTA (PADNE_B200_CO_R=16 for the taller block where it fits), 16 column warps + an
+    // inverter warp; PADNE_B200_INVERT=v1 keeps the round-1 kernel (16 rows, 256 threads).
+    static const bool invert_v1 = [] { const char *e = getenv("PADNE_B200_INVERT"); return e && strcmp(e, "v1") == 0; }();
+    int32_t R;
+    if (invert_v1) {
+        R = (int32_t)std::min<int64_t>(16, (int64_t)(200 * 1024) / ((int64_t)nc * 8));
+        if (const char *e = getenv("PADNE_B200_CO_R")) R = std::min<int32_t>(R, std::max(1, atoi(e)));   // tuning
+        R = std::max(R, (nc + ctx->n_sm - 1) / ctx->n_sm);
+    } else {
+        R = 12;
+        if (const char *e = getenv("PADNE_B200_CO_R")) R = atoi(e) == 16 ? 16 : 12;
+        if (R == 16 && (int64_t)nc * 16 * 8 > 205 * 1024) R = 12;
+    }
     if (R < 1 || R > 16) return fail("inverse: rows per CTA out of range");
     const int grid = (nc + R - 1) / R;
+    if (grid > ctx->n_sm) return fail("inverse: more row blocks than SMs");
     const size_t smem = (size_t)R * nc * sizeof(double);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        PDN_CUDA(cudaFuncSetAttribute(coarse_invert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(220 * 1024)));
-        smem_set = 220 * 1024;
+    if (smem > 205 * 1024) return fail("inverse: rows do not fit shared memory");
+    // columns per thread: one pass covers the matrix when nc <= 1536, else two passes of two
+    const int ncol = nc <= INV_BLK ? 1 : (nc <= 2 * INV_BLK ? 2 : (nc <= 3 * INV_BLK ? 3 : 2));
+    const void *kern = (const void *)coarse_invert_kernel;
+    if (!invert_v1) {
+        if (R == 12)
+            kern = ncol == 1 ? (const void *)coarse_invert2_kernel<1, 12>
+                 : ncol == 2 ? (const void *)coarse_invert2_kernel<2, 12> : (const void *)coarse_invert2_kernel<3, 12>;
+        else
+            kern = ncol == 1 ? (const void *)coarse_invert2_kernel<1, 16>
+                 : ncol == 2 ? (const void *)coarse_invert2_kernel<2, 16> : (const void *)coarse_invert2_kernel<3, 16>;
     }
-    if (smem > 220 * 1024) return fail("inverse: rows do not fit shared memory");
-    w->co_piv.reserve((size_t)grid * ((size_t)R * nc + 256));
-    w->co_counter.reserve((size_t)grid + 4);
-    PDN_CUDA(cudaMemsetAsync(w->co_counter.p, 0, ((size_t)grid + 4) * sizeof(unsigned int), st));
+    {
+        static const void *configured[8] = {};
+        const int slot = invert_v1 ? 0 : 1 + (R == 16 ? 3 : 0) + (ncol - 1);
+        if (configured[slot] != kern) {
+            PDN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(205 * 1024)));
+            configured[slot] = kern;
+        }
+    }
+    w->co_piv.reserve(((size_t)grid + 1) * ((size_t)R * nc + 256));
+    w->co_counter.reserve(2 * (size_t)grid + 4);
+    PDN_CUDA(cudaMemsetAsync(w->co_counter.p, 0, (2 * (size_t)grid + 4) * sizeof(unsigned int), st));
     pdn_status_reset(ctx);
     {
         int32_t nc_arg = nc, R_arg = R;
@@ -1564,8 +1587,10 @@ static bool build_coarse(pdn_ctx *ctx, SolveWork *w, int32_t target, int64_t n_e
         int32_t *st_arg = ctx->d_status;
         co_Af.reserve(nc2);
         float *af_arg = co_Af.p;
-        void *args[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg, &af_arg};
-        PDN_CUDA(cudaLaunchCooperativeKernel((void *)coarse_invert_kernel, dim3(grid), dim3(CO_BLK), args, smem, st));
+        void *args_v1[] = {&nc_arg, &R_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg, &af_arg};
+        void *args_v2[] = {&nc_arg, &A_arg, &piv_arg, &cnt_arg, &st_arg, &af_arg};
+        PDN_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(invert_v1 ? CO_BLK : INV_THREADS),
+                                             invert_v1 ? args_v1 : args_v2, smem, st));
         ctx->launches++;
     }
     int64_t detail = 0;
