@@ -70,7 +70,8 @@ typedef struct pdn_opts {
     int32_t method;     /* PDN_METHOD_*                                                            */
     int32_t precond;    /* PDN_PRECOND_*                                                           */
     int32_t check_every;/* iterations per CUDA-graph launch between host convergence polls; 0 -> 32 */
-    int64_t n_nodes;    /* voltage unknowns; <0 -> detect (trailing rows without a diagonal entry)  */
+    int64_t n_nodes;    /* voltage unknowns; <0 -> detect: the trailing rows without a diagonal entry that
+                           reference only earlier columns are the constraint rows                     */
     int32_t n_coarse;   /* target number of aggregates of the two-level preconditioner; 0 -> 1024 below
                            200 000 rows, 1600 above; capped at 1776                                    */
     int32_t reserved;

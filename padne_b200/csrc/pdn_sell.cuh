@@ -373,12 +373,10 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
         if (live) {
             if (EMODE == CG) xi = x[row];
             if (EMODE != PLAIN) ai = aux0[row];
-#ifndef PDN_DBG_NO_AGGLOAD
             if (MODE == CG2) {
                 a1 = __ldg(cg.agg + row);
                 if (cg.nc2 > 0) a2 = __ldg(cg.agg2 + row);
             }
-#endif
         }
         const int w = (off1 - off) >> 5;
         double sum = 0.0;
@@ -423,12 +421,10 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
             issue(jn);
             jn++;
         }
-#ifndef PDN_DBG_NO_RESTRICT
         if (MODE == CG2) {        // after the refill: the restriction runs while the next copies fly
             restrict_smem(sum, a1, fix, amin1, rtab, cg.tab);
             if (cg.nc2 > 0) restrict_smem(sum, a2, fix, amin2, rtab + 3 * TABW, cg.tab2);
         }
-#endif
     }
     __syncthreads();
     if (MODE == CG2) {
@@ -441,12 +437,8 @@ __global__ void __launch_bounds__(ST_BLK, PDN_SELL_TMINB) sell_tma_kernel(SellOp
     if (MODE == PLAIN) return;
     if (MODE == CG2) __threadfence();      // this thread's table atomics before the CTA's ticket
     if (!grid_reduce<3, ST_WARPS>(acc, partials, &sc->ticket[0], red)) return;
-#ifdef PDN_DBG_PLAIN_TAIL
-    dots_tail<EMODE, DIST>(acc, sc, Lp);
-#else
     if (MODE == CG2) cg2_tail<DIST>(acc, sc, cg, Lp, fix);
     else dots_tail<EMODE, DIST>(acc, sc, Lp);
-#endif
 }
 
 // [first, last] aggregate among the rows [row_begin, row_end): range[0] starts at INT_MAX, range[1] at -1

@@ -1220,11 +1220,15 @@ namespace {
 
 __global__ void __launch_bounds__(BLK) last_diag_kernel(int64_t N, const int32_t *__restrict__ rp,
                                                         const int32_t *__restrict__ ci, int32_t *out) {
-    // out = 1 + largest row index that stores a diagonal entry
+    // out[0] = 1 + largest row index that stores a diagonal entry;
+    // out[1] = 1 + largest row index WITHOUT a diagonal that has an entry right of the diagonal position: an internal
+    // node touched only by voltage sources (its row holds nothing but +-1 in source-current columns, which lie after
+    // it), whereas a constraint row only references node columns, all of them before it.  n_nodes = max of the two.
     for (int64_t i = (int64_t)blockIdx.x * BLK + threadIdx.x; i < N; i += (int64_t)gridDim.x * BLK) {
-        bool has = false;
-        for (int32_t k = rp[i]; k < rp[i + 1]; k++) has = has || ci[k] == i;
+        bool has = false, upper = false;
+        for (int32_t k = rp[i]; k < rp[i + 1]; k++) { has = has || ci[k] == i; upper = upper || ci[k] > i; }
         if (has) atomicMax(out, (int32_t)i + 1);
+        else if (upper) atomicMax(out + 1, (int32_t)i + 1);
     }
 }
 
@@ -1708,12 +1712,12 @@ void pdn_solve_impl(pdn_ctx *ctx, const double *rhs, const pdn_opts *opts_in, do
     int64_t n = opts.n_nodes;
     if (n < 0) {
         w->tmp_i32a.reserve(4);
-        PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, sizeof(int32_t), st));
+        PDN_CUDA(cudaMemsetAsync(w->tmp_i32a.p, 0, 2 * sizeof(int32_t), st));
         PDN_LAUNCH(ctx, last_diag_kernel, pdn_grid(ctx, N, BLK, 8), BLK, 0, N, L.indptr.p, L.indices.p, w->tmp_i32a.p);
-        int32_t n32 = 0;
-        PDN_CUDA(cudaMemcpyAsync(&n32, w->tmp_i32a.p, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        int32_t n32[2] = {0, 0};
+        PDN_CUDA(cudaMemcpyAsync(n32, w->tmp_i32a.p, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         PDN_CUDA(cudaStreamSynchronize(st));
-        n = n32;
+        n = std::max(n32[0], n32[1]);
     }
     if (n <= 0 || n > N) PDN_FAIL(PDN_EINVAL, "solve: n_nodes = %lld out of range (N = %lld)", (long long)n, (long long)N);
     const int m = (int)(N - n);

@@ -10,6 +10,7 @@ import os
 import numpy as np
 import pytest
 import scipy.sparse
+import scipy.sparse.linalg
 
 from conftest import golden_laplace_files, golden_system_files, load_system
 from oracle import oracle
@@ -211,6 +212,31 @@ def test_solve_autodetects_n_nodes_and_accepts_foreign_csr(ctx):
     ctx.set_csr(d["indptr"], d["indices"], d["data"])
     v, info = ctx.solve(d["r"])                         # n_nodes = -1 -> detected from the diagonal
     assert voltage_error(v, d["v"], fs.n_nodes) <= VOLTAGE_RTOL
+
+
+def test_autodetect_with_an_internal_node_that_only_sources_touch(ctx):
+    # ADVICE (round 1): an internal node between two voltage sources in series has no diagonal entry; as the LAST
+    # internal node it used to be taken for a constraint row.  Small resistor ladder 0..4, node 5 internal:
+    # source A: node 0 -> 5 (1 V), source B: node 5 -> 4 (0.5 V), ground at node 4.  Stamps as padne/solver.py:469-560.
+    n, m = 6, 2
+    N = n + m + 1
+    L = scipy.sparse.lil_matrix((N, N))
+    r = np.zeros(N)
+    for a in range(4):                                   # conductances on the chain 0-1-2-3-4
+        g = 1.0 + a
+        L[a, a] -= g; L[a + 1, a + 1] -= g; L[a, a + 1] += g; L[a + 1, a] += g
+    for k, (p_, q_, volt) in enumerate([(0, 5, 1.0), (5, 4, 0.5)]):
+        c = n + k
+        L[p_, c] += 1.0; L[q_, c] -= 1.0; L[c, p_] = 1.0; L[c, q_] = -1.0; r[c] = volt
+    L[4, N - 1] = 1.0; L[N - 1, 4] = 1.0
+    A = L.tocsr(); A.sort_indices()
+    assert A[5, 5] == 0.0                                # the internal node stores no diagonal
+    ctx.set_csr(A.indptr.astype(np.int32), A.indices.astype(np.int32), A.data)
+    v, info = ctx.solve(r)                               # n_nodes = -1 -> detected
+    v_ref = scipy.sparse.linalg.spsolve(A.tocsc(), r)
+    assert np.allclose(v, v_ref, rtol=1e-9, atol=1e-12)
+    v2, _ = ctx.solve(r, n_nodes=n)
+    assert np.array_equal(v, v2)
 
 
 def test_solve_voltage_source_loop_is_singular(ctx):
