@@ -1011,7 +1011,14 @@ KrylovResult run_krylov(pdn_ctx *ctx, SolveWork *w, int method, KrylovTarget tgt
         per_iter = (int)((ctx->launches - launches_before) / check_every);   // kernels of one captured iteration
         ctx->launches = launches_before;  // capture is not execution
     };
-    build_graph();
+    {
+        const auto tb0 = std::chrono::steady_clock::now();
+        build_graph();
+        if (getenv("PADNE_B200_TRACE"))
+            fprintf(stderr, "[padne_b200 trace rank %d] graph capture + instantiate: %.3f ms (%d kernels per iteration x %d)\n",
+                    pdn_comm_rank(ctx), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tb0).count(),
+                    per_iter, check_every);
+    }
 
     auto cleanup = [&]() {
         if (exec) cudaGraphExecDestroy(exec);
