@@ -181,3 +181,32 @@ def test_node_indexer_create_with_batched_lookup():
         assert "_construct_kdtrees" in ref.NodeIndexer.__dict__            # the reference class is restored
         again = ref.NodeIndexer.create(prob, meshes, m2l, vindex, nets)
         assert again.node_to_global_index == stock.node_to_global_index
+
+
+def test_solve_system_warns_only_when_the_requested_rtol_is_missed():
+    # ADVICE (round 1): a caller asking for rtol must be told when the iteration stopped above it.  The C ABI accepts
+    # stagnation only at the fp64 floor (pdn_info.stagnated); the Python mirror turns "stagnated AND above rtol" into
+    # a SolverWarning and stays silent otherwise, like the reference's direct solve (padne/solver.py:767-780).
+    import dataclasses
+    import warnings
+    from oracle_context import OracleContext
+    from padne_b200 import solver as S
+
+    class Stagnating(OracleContext):
+        def __init__(self, rel, stagnated):
+            super().__init__()
+            self.rel, self.stag = rel, stagnated
+
+        def solve(self, rhs, n_nodes=-1, **opts):
+            v, info = super().solve(rhs, n_nodes, **opts)
+            return v, dataclasses.replace(info, rel_residual=self.rel, stagnated=self.stag, floor_abs=1e-9, rhs_norm=2e3)
+
+    fs, d = load_system(golden_system_files()[0])
+    L = scipy.sparse.csr_matrix((d["data"], d["indices"], d["indptr"]), shape=(fs.N, fs.N))
+    for rel, stag, expect in ((3e-10, 1, True), (5e-11, 1, False), (3e-10, 0, False)):
+        with warnings.catch_warnings(record=True) as rec:
+            warnings.simplefilter("always")
+            v, info = S.solve_system(L, d["r"], ctx=Stagnating(rel, stag), n_nodes=fs.n_nodes)
+        hit = [w for w in rec if issubclass(w.category, S.SolverWarning) and "stagnated" in str(w.message)]
+        assert bool(hit) == expect, (rel, stag, [str(w.message) for w in rec])
+        assert np.allclose(v, d["v"], rtol=1e-9, atol=1e-12) and info.residual_norm < 1e-9
